@@ -1,0 +1,136 @@
+// common.cuh - shared declarations for the kernels and the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "g1.cuh"
+
+namespace fb {
+
+constexpr int kNumSMs = 148;  // B200
+extern unsigned long long g_launches;  // kernel launches issued by this library (api.cu)
+
+struct CudaError {
+    std::string msg;
+};
+
+#define FB_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess) {                                                                        \
+            char _b[512];                                                                               \
+            snprintf(_b, sizeof _b, "CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, __LINE__, \
+                     cudaGetErrorString(_e));                                                           \
+            throw fb::CudaError{_b};                                                                    \
+        }                                                                                               \
+    } while (0)
+
+// grow-only device scratch buffer
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* get(size_t bytes) {
+        if (bytes > cap) {
+            if (p) FB_CUDA(cudaFree(p));
+            p = nullptr;
+            cap = 0;
+            size_t want = bytes + bytes / 8 + 256;
+            FB_CUDA(cudaMalloc(&p, want));
+            cap = want;
+        }
+        return p;
+    }
+    template <class T>
+    T* as(size_t count) { return (T*)get(count * sizeof(T)); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// ---------------------------------------------------------------- NTT (ntt.cu)
+// Twiddle tables for one transform size N = 2^log_n (Montgomery form, device).
+struct NttTables {
+    int log_n = -1;
+    int lo_bits = 0;           // w^e = hi[e >> lo_bits] * lo[e & (2^lo_bits - 1)]
+    Fr* lo[2] = {nullptr, nullptr};   // [0] forward, [1] inverse
+    Fr* hi[2] = {nullptr, nullptr};   // inverse hi table is pre-scaled by 1/N
+    Fr* hi_unscaled_inv = nullptr;    // inverse hi table without the 1/N factor
+    Fr* consts = nullptr;             // device: [0] w_N, [1] w_N^-1, [2] 1/N
+};
+
+struct NttPlan {
+    int npass = 0;
+    int log_r[4] = {0, 0, 0, 0};
+};
+
+void ntt_build_tables(NttTables& t, int log_n, cudaStream_t st);
+void ntt_free_tables(NttTables& t);
+// tile twiddles w_R^j (j < R/2) for every radix 2^1..2^10, forward and inverse
+struct TileTwiddles {
+    Fr* base[2] = {nullptr, nullptr};  // entry for radix log_r starts at offset (1<<(log_r-1)) - 1
+};
+void ntt_build_tile_twiddles(TileTwiddles& t, cudaStream_t st);
+NttPlan ntt_make_plan(int log_n);
+// out may alias in; scratch must hold N elements when the plan has >= 2 passes
+void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out, Fr* scratch, bool inverse,
+             cudaStream_t st);
+
+// -------------------------------------------------------------- poly (poly.cu)
+// wire <-> device conversions and the Horner/quotient scan
+void fr_from_be(const uint8_t* d_in, Fr* d_out, size_t n, int* d_err, cudaStream_t st);  // sets *d_err=1 on >= r
+void fr_to_be(const Fr* d_in, uint8_t* d_out, size_t n, cudaStream_t st);
+void fr_fill_zero(Fr* d, size_t n, cudaStream_t st);
+// s_k = a_k + x*s_{k+1} (suffix Horner scan), s_n = 0.  Writes y = s_0 to d_y and,
+// when d_q != nullptr, q_k = s_{k+1} for k < n-1 and q_{n-1} = 0 (the zero-padded
+// quotient (p - y)/(X - x)).  d_x, d_y are single device Fr (Montgomery).
+void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st);
+
+// ---------------------------------------------------------------- MSM (msm.cu)
+struct MsmBases {
+    G1Affine* pts = nullptr;  // [rows][nwin][n] when tabulated (window w holds 2^(c*w) * P), else [rows][n]
+    size_t n = 0;             // row length
+    int c = 0;                // window bits of the table (0: no table)
+    int nwin = 0;
+};
+
+struct MsmScratch {
+    DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc;
+};
+
+// d_out[b] (device XYZZ) = sum_k scalars[b*len + k] * bases_b[k] for b < batch, where
+// row b's bases start at pts + b*(nwin or 1)*bases.n.  Scalars are device Fr either
+// in Montgomery form (scalars_mont) or canonical little-endian limbs.
+void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
+             MsmScratch& s, cudaStream_t st);
+// table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin
+void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, G1Affine* d_out, DevBuf& scratch,
+                     cudaStream_t st);
+int msm_pick_window(size_t n, bool tabulated);
+
+// -------------------------------------------------------------- points (g1ops.cu)
+void g1_decompress_batch(const uint8_t* d_in48, G1Affine* d_out, size_t n, int* d_err, cudaStream_t st);
+void g1_deserialize_batch(const uint8_t* d_in96, G1Affine* d_out, size_t n, int* d_err, cudaStream_t st);
+void g1_compress_batch(const G1Affine* d_in, uint8_t* d_out48, size_t n, cudaStream_t st);
+void g1_serialize_batch(const G1Affine* d_in, uint8_t* d_out96, size_t n, cudaStream_t st);
+void g1_xyzz_to_affine_batch(const G1Xyzz* d_in, G1Affine* d_out, size_t n, cudaStream_t st);
+// out[k] = scalars[k] * G (fixed-base comb on the generator), scalars Montgomery Fr
+void g1_fixed_base_mul(const Fr* d_scalars, size_t n, G1Affine* d_out, DevBuf& scratch, cudaStream_t st);
+// d_out (1 XYZZ) = sum of n affine points (tree sum)
+void g1_sum_affine(const G1Affine* d_in, size_t n, G1Xyzz* d_out, DevBuf& scratch, cudaStream_t st);
+
+
+// ------------------------------------------------------------------ SRS (srs.cu)
+void srs_secret_to_fr(const uint8_t* d_secret32, Fr* d_out, cudaStream_t st);
+void srs_lagrange_at(const Fr* d_tau, int log_n, Fr* d_out, Fr* d_hdr3, cudaStream_t st);
+void srs_powers(const Fr* d_tau, size_t n, Fr* d_out, cudaStream_t st);
+void srs_outer(const Fr* d_r, size_t nrows, const Fr* d_l, size_t T, Fr* d_out, cudaStream_t st);
+
+}  // namespace fb

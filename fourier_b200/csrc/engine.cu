@@ -1,0 +1,448 @@
+// engine.cu - the PianoBackend calls of the C ABI: SRS residency and the
+// worker / master commit + open paths (reference src/engine/piano.rs:143-298,
+// 587-846, 883-1037).
+#include <string.h>
+
+#include <fstream>
+
+#include "ctx.cuh"
+
+namespace fb {
+Fr* ctx_upload_fr(fb_ctx* c, DevBuf& bytes, DevBuf& dst, const uint8_t* h_be, size_t count);
+void ctx_reset_err(fb_ctx* c);
+int ctx_check_err(fb_ctx* c);
+void ctx_points_out(fb_ctx* c, const G1Xyzz* d_xyzz, size_t count, uint8_t* d_out48);
+bool g2_generate_host(const uint8_t sx[32], const uint8_t sy[32], std::vector<uint8_t> out[3]);  // g2host.cpp
+bool g2_recode_host(const std::vector<uint8_t>& in, bool to_compressed, std::vector<uint8_t>& out);
+}  // namespace fb
+
+using namespace fb;
+
+namespace {
+
+void srs_free(fb_ctx* c) {
+    if (c->u_bases.pts && c->u_bases.pts != c->d_u) cudaFree(c->u_bases.pts);
+    if (c->y_bases.pts && c->y_bases.pts != c->d_g_tau_y) cudaFree(c->y_bases.pts);
+    if (c->d_u) cudaFree(c->d_u);
+    if (c->d_g_tau_x) cudaFree(c->d_g_tau_x);
+    if (c->d_g_tau_y) cudaFree(c->d_g_tau_y);
+    c->d_u = c->d_g_tau_x = c->d_g_tau_y = nullptr;
+    c->u_bases = MsmBases();
+    c->y_bases = MsmBases();
+    c->srs_ready = false;
+}
+
+// build the resident window tables (PianoPrecomputation::generate, piano.rs:477-504)
+void srs_build_tables(fb_ctx* c) {
+    c->u_bases = MsmBases();
+    c->u_bases.n = c->T;
+    c->u_bases.pts = c->d_u;
+    c->y_bases = MsmBases();
+    c->y_bases.n = c->M;
+    c->y_bases.pts = c->d_g_tau_y;
+    if (c->window_pref < 0) return;
+    if (c->T >= 16) {
+        int cc = c->window_pref > 0 ? c->window_pref : msm_pick_window(c->T, true);
+        int nwin = (256 + cc - 1) / cc;
+        G1Affine* tab;
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->T * c->nrows * sizeof(G1Affine)));
+        msm_build_table(c->d_u, c->T, c->nrows, cc, nwin, tab, c->pt_a, c->stream);
+        c->u_bases.pts = tab;
+        c->u_bases.c = cc;
+        c->u_bases.nwin = nwin;
+    }
+    if (c->M >= 16) {
+        int cc = msm_pick_window(c->M, true);
+        int nwin = (256 + cc - 1) / cc;
+        G1Affine* tab;
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->M * sizeof(G1Affine)));
+        msm_build_table(c->d_g_tau_y, c->M, 1, cc, nwin, tab, c->pt_a, c->stream);
+        c->y_bases.pts = tab;
+        c->y_bases.c = cc;
+        c->y_bases.nwin = nwin;
+    }
+    FB_CUDA(cudaStreamSynchronize(c->stream));
+}
+
+int check_rows(fb_ctx* c, uint64_t& row0, uint64_t& nrows) {
+    if (nrows == 0) {
+        row0 = 0;
+        nrows = c->M;
+    }
+    if (row0 + nrows > c->M) return ctx_fail(c, FB_ERR_ARG, "row range exceeds 2^machines_scale");
+    return FB_OK;
+}
+
+MsmBases row_bases(fb_ctx* c, uint64_t i) {
+    MsmBases b = c->u_bases;
+    size_t per_row = (size_t)(b.c > 0 ? b.nwin : 1) * c->T;
+    b.pts = c->u_bases.pts + (i - c->row0) * per_row;
+    return b;
+}
+
+int need_row(fb_ctx* c, uint64_t i, uint64_t cnt) {
+    if (!c->srs_ready) return ctx_fail(c, FB_ERR_STATE, "setup not loaded");
+    if (i + cnt > c->M) return ctx_fail(c, FB_ERR_ARG, "machine index out of range");
+    if (i < c->row0 || i + cnt > c->row0 + c->nrows) return ctx_fail(c, FB_ERR_STATE, "row not resident on this context");
+    return FB_OK;
+}
+
+// the field half of worker_open on device: d_coeffs (Montgomery, len) ->
+// y (d_y) and q_hat = NTT(q || 0) in c->fr_b.  Returns q_hat.
+Fr* open_scalars(fb_ctx* c, const NttTables& tab, const Fr* d_coeffs, size_t len, const Fr* d_alpha, Fr* d_y) {
+    Fr* d_poly = c->fr_b.as<Fr>(len);
+    Fr* d_tmp = c->fr_c.as<Fr>(len);
+    ntt_run(tab, c->tile_tw, d_coeffs, d_poly, d_tmp, true, c->stream);          // piano.rs:194
+    Fr* d_q = c->fr_a.as<Fr>(len);  // NB: callers keep d_coeffs elsewhere or accept the overwrite
+    horner_quotient(d_poly, len, d_alpha, d_y, d_q, c->scan, c->stream);           // :202-225
+    ntt_run(tab, c->tile_tw, d_q, d_poly, d_tmp, false, c->stream);               // :233
+    return d_poly;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fb_srs_generate(fb_ctx* c, const uint8_t sx[32], const uint8_t sy[32], uint64_t row0, uint64_t nrows) {
+    return ctx_call(c, [&]() -> int {
+        int rc = check_rows(c, row0, nrows);
+        if (rc) return rc;
+        srs_free(c);
+        c->row0 = row0;
+        c->nrows = nrows;
+        cudaStream_t st = c->stream;
+        uint8_t* d_sec = c->in_bytes.as<uint8_t>(64);
+        FB_CUDA(cudaMemcpyAsync(d_sec, sx, 32, cudaMemcpyHostToDevice, st));
+        FB_CUDA(cudaMemcpyAsync(d_sec + 32, sy, 32, cudaMemcpyHostToDevice, st));
+        Fr* d_small = c->small.as<Fr>(16);  // [0] tau_x [1] tau_y [2..4] hdr
+        srs_secret_to_fr(d_sec, d_small, st);
+        srs_secret_to_fr(d_sec + 32, d_small + 1, st);
+        Fr* d_l = c->fr_a.as<Fr>(c->T);
+        Fr* d_r = c->fr_b.as<Fr>(c->M);
+        srs_lagrange_at(d_small, (int)c->t, d_l, d_small + 2, st);      // piano.rs:973-988
+        srs_lagrange_at(d_small + 1, (int)c->m, d_r, d_small + 5, st);  // :956-971
+        FB_CUDA(cudaMalloc(&c->d_u, nrows * c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_g_tau_x, c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_g_tau_y, c->M * sizeof(G1Affine)));
+        // U[i][j] = g^(R_i * L_j)  (:995-1007), in slabs of rows to bound the scalar scratch
+        size_t slab = ((size_t)1 << 22) / c->T;
+        if (slab < 1) slab = 1;
+        for (uint64_t r = 0; r < nrows; r += slab) {
+            size_t rc2 = nrows - r < slab ? nrows - r : slab;
+            Fr* d_prod = c->fr_c.as<Fr>(rc2 * c->T);
+            srs_outer(d_r + row0 + r, rc2, d_l, c->T, d_prod, st);
+            g1_fixed_base_mul(d_prod, rc2 * c->T, c->d_u + r * c->T, c->pt_a, st);
+        }
+        {
+            Fr* d_pw = c->fr_c.as<Fr>(c->T > c->M ? c->T : c->M);
+            srs_powers(d_small, c->T, d_pw, st);  // :916-931
+            g1_fixed_base_mul(d_pw, c->T, c->d_g_tau_x, c->pt_a, st);
+            srs_powers(d_small + 1, c->M, d_pw, st);  // :934-949
+            g1_fixed_base_mul(d_pw, c->M, c->d_g_tau_y, c->pt_a, st);
+        }
+        c->g = g1_generator();
+        FB_CUDA(cudaStreamSynchronize(st));
+        g2_generate_host(sx, sy, c->g2_bytes);
+        c->g2_compressed = 1;
+        srs_build_tables(c);
+        c->srs_ready = true;
+        return FB_OK;
+    });
+}
+
+int fb_srs_load_bytes(fb_ctx* c, const uint8_t* buf, size_t len, int compressed, uint64_t row0, uint64_t nrows) {
+    return ctx_call(c, [&]() -> int {
+        int rc = check_rows(c, row0, nrows);
+        if (rc) return rc;
+        const size_t e1 = compressed ? 48 : 96, e2 = compressed ? 96 : 192;
+        size_t pos = 0;
+        auto need = [&](size_t k) { return pos + k <= len; };
+        auto rd64 = [&](uint64_t& v) {
+            if (!need(8)) return false;
+            memcpy(&v, buf + pos, 8);  // u64 little-endian (piano.rs:671-673)
+            pos += 8;
+            return true;
+        };
+        const char* trunc = "failed to fill whole buffer";
+        if (!need(e1)) return ctx_fail(c, FB_ERR_IO, trunc);
+        size_t off_g = pos;
+        pos += e1;
+        uint64_t nx, ny, rows, cols;
+        if (!rd64(nx) || !need(nx * e1)) return ctx_fail(c, FB_ERR_IO, trunc);
+        size_t off_x = pos;
+        pos += nx * e1;
+        if (!rd64(ny) || !need(ny * e1)) return ctx_fail(c, FB_ERR_IO, trunc);
+        size_t off_y = pos;
+        pos += ny * e1;
+        if (!rd64(rows) || !rd64(cols) || !need(rows * cols * e1)) return ctx_fail(c, FB_ERR_IO, trunc);
+        size_t off_u = pos;
+        pos += rows * cols * e1;
+        if (!need(3 * e2)) return ctx_fail(c, FB_ERR_IO, trunc);
+        if (nx != c->T || ny != c->M || rows != c->M || cols != c->T)
+            return ctx_fail(c, FB_ERR_ARG, "setup dimensions do not match scale / machines_scale");
+        srs_free(c);
+        c->row0 = row0;
+        c->nrows = nrows;
+        cudaStream_t st = c->stream;
+        ctx_reset_err(c);
+        FB_CUDA(cudaMalloc(&c->d_u, nrows * c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_g_tau_x, c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_g_tau_y, c->M * sizeof(G1Affine)));
+        auto decode = [&](size_t off, size_t count, G1Affine* dst) {
+            // upload in slabs of <= 64 MiB and decode on the GPU
+            const size_t slab = ((size_t)64 << 20) / e1;
+            for (size_t k = 0; k < count; k += slab) {
+                size_t cnt = count - k < slab ? count - k : slab;
+                uint8_t* d_b = c->in_bytes.as<uint8_t>(cnt * e1 + 16);
+                FB_CUDA(cudaMemcpyAsync(d_b, buf + off + k * e1, cnt * e1, cudaMemcpyHostToDevice, st));
+                if (compressed) g1_decompress_batch(d_b, dst + k, cnt, c->d_err + 1, st);
+                else g1_deserialize_batch(d_b, dst + k, cnt, c->d_err + 1, st);
+            }
+        };
+        G1Affine* d_g = c->pt_b.as<G1Affine>(2);
+        decode(off_g, 1, d_g);
+        decode(off_x, c->T, c->d_g_tau_x);
+        decode(off_y, c->M, c->d_g_tau_y);
+        decode(off_u + row0 * c->T * e1, nrows * c->T, c->d_u);
+        FB_CUDA(cudaMemcpyAsync(&c->g, d_g, sizeof(G1Affine), cudaMemcpyDeviceToHost, st));
+        rc = ctx_check_err(c);
+        if (rc) {
+            srs_free(c);
+            return rc;
+        }
+        for (int k = 0; k < 3; k++) c->g2_bytes[k].assign(buf + pos + k * e2, buf + pos + (k + 1) * e2);
+        c->g2_compressed = compressed ? 1 : 0;
+        srs_build_tables(c);
+        c->srs_ready = true;
+        return FB_OK;
+    });
+}
+
+int fb_srs_load_file(fb_ctx* c, const char* path, int compressed, uint64_t row0, uint64_t nrows) {
+    if (!c || !path) return FB_ERR_ARG;
+    std::vector<uint8_t> data;
+    {
+        std::ifstream f(path, std::ios::binary | std::ios::ate);
+        if (!f) {
+            std::lock_guard<std::mutex> lk(c->mu);
+            return ctx_fail(c, FB_ERR_IO, std::string("cannot open ") + path);
+        }
+        std::streamsize sz = f.tellg();
+        f.seekg(0);
+        data.resize((size_t)sz);
+        if (sz && !f.read((char*)data.data(), sz)) {
+            std::lock_guard<std::mutex> lk(c->mu);
+            return ctx_fail(c, FB_ERR_IO, std::string("cannot read ") + path);
+        }
+    }
+    return fb_srs_load_bytes(c, data.data(), data.size(), compressed, row0, nrows);
+}
+
+int fb_srs_to_bytes(fb_ctx* c, int compressed, uint8_t* out, size_t cap, size_t* written) {
+    return ctx_call(c, [&]() -> int {
+        if (!c->srs_ready) return ctx_fail(c, FB_ERR_STATE, "setup not loaded");
+        if (c->row0 != 0 || c->nrows != c->M) return ctx_fail(c, FB_ERR_STATE, "saving needs every row resident");
+        const size_t e1 = compressed ? 48 : 96, e2 = compressed ? 96 : 192;
+        size_t total = e1 + 8 + c->T * e1 + 8 + c->M * e1 + 16 + c->M * c->T * e1 + 3 * e2;
+        if (written) *written = total;
+        if (!out) return FB_OK;
+        if (cap < total) return ctx_fail(c, FB_ERR_ARG, "output buffer too small");
+        cudaStream_t st = c->stream;
+        size_t pos = 0;
+        auto encode = [&](const G1Affine* src, size_t count) {
+            const size_t slab = ((size_t)64 << 20) / e1;
+            for (size_t k = 0; k < count; k += slab) {
+                size_t cnt = count - k < slab ? count - k : slab;
+                uint8_t* d_b = c->out_bytes.as<uint8_t>(cnt * e1);
+                if (compressed) g1_compress_batch(src + k, d_b, cnt, st);
+                else g1_serialize_batch(src + k, d_b, cnt, st);
+                FB_CUDA(cudaMemcpyAsync(out + pos, d_b, cnt * e1, cudaMemcpyDeviceToHost, st));
+                FB_CUDA(cudaStreamSynchronize(st));
+                pos += cnt * e1;
+            }
+        };
+        auto wr64 = [&](uint64_t v) {
+            memcpy(out + pos, &v, 8);
+            pos += 8;
+        };
+        G1Affine* d_g = c->pt_b.as<G1Affine>(2);
+        FB_CUDA(cudaMemcpyAsync(d_g, &c->g, sizeof(G1Affine), cudaMemcpyHostToDevice, st));
+        encode(d_g, 1);
+        wr64(c->T);
+        encode(c->d_g_tau_x, c->T);
+        wr64(c->M);
+        encode(c->d_g_tau_y, c->M);
+        wr64(c->M);
+        wr64(c->T);
+        encode(c->d_u, c->M * c->T);
+        for (int k = 0; k < 3; k++) {
+            std::vector<uint8_t> tmp;
+            const std::vector<uint8_t>* src = &c->g2_bytes[k];
+            if ((c->g2_compressed != 0) != (compressed != 0)) {
+                if (!g2_recode_host(c->g2_bytes[k], compressed != 0, tmp)) return ctx_fail(c, FB_ERR_STATE, "bad G2 element");
+                src = &tmp;
+            }
+            if (src->size() != e2) return ctx_fail(c, FB_ERR_STATE, "G2 elements unavailable");
+            memcpy(out + pos, src->data(), e2);
+            pos += e2;
+        }
+        return FB_OK;
+    });
+}
+
+int fb_srs_save_file(fb_ctx* c, const char* path, int compressed) {
+    if (!c || !path) return FB_ERR_ARG;
+    size_t total = 0;
+    int rc = fb_srs_to_bytes(c, compressed, nullptr, 0, &total);
+    if (rc) return rc;
+    std::vector<uint8_t> data(total);
+    rc = fb_srs_to_bytes(c, compressed, data.data(), total, &total);
+    if (rc) return rc;
+    std::ofstream f(path, std::ios::binary | std::ios::trunc);
+    if (!f || !f.write((const char*)data.data(), (std::streamsize)total)) {
+        std::lock_guard<std::mutex> lk(c->mu);
+        return ctx_fail(c, FB_ERR_IO, std::string("cannot write ") + path);
+    }
+    return FB_OK;
+}
+
+// ---------------------------------------------------------------- worker side
+int fb_commit_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len, uint8_t* out48s) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, row0, nrows);
+        if (rc) return rc;
+        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
+        if (nrows == 0) return FB_OK;
+        ctx_reset_err(c);
+        Fr* d_s = ctx_upload_fr(c, c->in_bytes, c->fr_a, coeffs_be, nrows * len);
+        G1Xyzz* d_r = c->small.as<G1Xyzz>(nrows + 1);
+        msm_run(row_bases(c, row0), d_s, len, nrows, true, d_r, c->msm, c->stream);  // piano.rs:150-158
+        uint8_t* d_ob = c->out_bytes.as<uint8_t>(48 * nrows);
+        ctx_points_out(c, d_r, nrows, d_ob);
+        FB_CUDA(cudaMemcpyAsync(out48s, d_ob, 48 * nrows, cudaMemcpyDeviceToHost, c->stream));
+        return ctx_check_err(c);
+    });
+}
+
+int fb_worker_commit(fb_ctx* c, uint64_t i, const uint8_t* coeffs_be, uint64_t len, uint8_t out48[48]) {
+    return fb_commit_rows(c, i, 1, coeffs_be, len, out48);
+}
+
+int fb_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                 uint8_t* out_ys_be, uint8_t* out_proof48s) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, row0, nrows);
+        if (rc) return rc;
+        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "Supplied list is longer than the available max width");
+        int lg = ilog2_exact(len);
+        if (lg < 0) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+        if (nrows == 0) return FB_OK;
+        ctx_reset_err(c);
+        const NttTables& tab = ctx_ntt_tables(c, lg);
+        // all rows' coefficients go up in one copy; rows are then processed in turn
+        uint8_t* d_b = c->in_bytes.as<uint8_t>(nrows * len * 32 + 64);
+        FB_CUDA(cudaMemcpyAsync(d_b, coeffs_be, nrows * len * 32, cudaMemcpyHostToDevice, c->stream));
+        Fr* d_alpha = ctx_upload_fr(c, c->small, c->pt_a, alpha_be, 1);
+        Fr* d_all = (Fr*)c->msm.misc.get((nrows * len + nrows + 1) * sizeof(Fr));
+        Fr* d_ys = d_all + nrows * len;
+        fr_from_be(d_b, d_all, nrows * len, c->d_err, c->stream);
+        G1Xyzz* d_r = (G1Xyzz*)c->msm.order.get((nrows + 1) * sizeof(G1Xyzz));
+        for (uint64_t r = 0; r < nrows; r++) {
+            Fr* d_qhat = open_scalars(c, tab, d_all + r * len, len, d_alpha, d_ys + r);
+            msm_run(row_bases(c, row0 + r), d_qhat, len, 1, true, d_r + r, c->msm, c->stream);  // piano.rs:228-236
+        }
+        uint8_t* d_ob = c->out_bytes.as<uint8_t>(80 * nrows);
+        ctx_points_out(c, d_r, nrows, d_ob + 32 * nrows);
+        fr_to_be(d_ys, d_ob, nrows, c->stream);
+        FB_CUDA(cudaMemcpyAsync(out_ys_be, d_ob, 32 * nrows, cudaMemcpyDeviceToHost, c->stream));
+        FB_CUDA(cudaMemcpyAsync(out_proof48s, d_ob + 32 * nrows, 48 * nrows, cudaMemcpyDeviceToHost, c->stream));
+        return ctx_check_err(c);
+    });
+}
+
+int fb_worker_open(fb_ctx* c, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                   uint8_t out_y_be[32], uint8_t out_proof48[48]) {
+    return fb_open_rows(c, i, 1, coeffs_be, len, alpha_be, out_y_be, out_proof48);
+}
+
+// ---------------------------------------------------------------- master side
+int fb_master_commit(fb_ctx* c, const uint8_t* commitments48, uint64_t count, uint8_t out48[48]) {
+    return fb_g1_sum(c, commitments48, count, 48, out48);  // all-ones MSM == point sum (piano.rs:164-175)
+}
+
+int fb_master_open(fb_ctx* c, const uint8_t* evals_be, const uint8_t* proofs48, uint64_t count, const uint8_t beta_be[32],
+                   uint8_t out_z_be[32], uint8_t out_pi0_48[48], uint8_t out_pi1_48[48]) {
+    return ctx_call(c, [&]() -> int {
+        if (!c->srs_ready) return ctx_fail(c, FB_ERR_STATE, "setup not loaded");
+        if (count > c->M) return ctx_fail(c, FB_ERR_ARG, "Supplied list is longer than the available max width");
+        int lg = ilog2_exact(count);
+        if (lg < 0) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+        ctx_reset_err(c);
+        cudaStream_t st = c->stream;
+        // pi_0 = sum of the worker proofs (piano.rs:258-265)
+        uint8_t* d_pb = c->in_bytes.as<uint8_t>(count * 48 + 16);
+        FB_CUDA(cudaMemcpyAsync(d_pb, proofs48, count * 48, cudaMemcpyHostToDevice, st));
+        G1Affine* pts = c->pt_a.as<G1Affine>(count + 1);
+        g1_decompress_batch(d_pb, pts, count, c->d_err + 1, st);
+        G1Xyzz* d_r = (G1Xyzz*)c->msm.order.get(4 * sizeof(G1Xyzz));
+        g1_sum_affine(pts, count, d_r, c->scan, st);
+        // f(Y, alpha) = iNTT_right(evals); z = f(beta); q1 = (f - z)/(Y - beta)  (:268-282)
+        const NttTables& tab = ctx_ntt_tables(c, lg);
+        Fr* d_ev = ctx_upload_fr(c, c->in_bytes, c->fr_a, evals_be, count);
+        Fr* d_beta = (Fr*)c->msm.misc.get(4 * sizeof(Fr));
+        {
+            uint8_t* d_bb = c->small.as<uint8_t>(64);
+            FB_CUDA(cudaMemcpyAsync(d_bb, beta_be, 32, cudaMemcpyHostToDevice, st));
+            fr_from_be(d_bb, d_beta, 1, c->d_err, st);
+        }
+        Fr* d_z = d_beta + 1;
+        Fr* d_poly = c->fr_b.as<Fr>(count);
+        Fr* d_tmp = c->fr_c.as<Fr>(count);
+        ntt_run(tab, c->tile_tw, d_ev, d_poly, d_tmp, true, st);
+        horner_quotient(d_poly, count, d_beta, d_z, d_ev, c->scan, st);  // q (zero-padded) overwrites evals
+        // pi_1 = sum_j q_j * g^(tau_Y^j)  (:286-295)
+        msm_run(c->y_bases, d_ev, count, 1, true, d_r + 1, c->msm, st);
+        uint8_t* d_ob = c->out_bytes.as<uint8_t>(32 + 96);
+        fr_to_be(d_z, d_ob, 1, st);
+        ctx_points_out(c, d_r, 2, d_ob + 32);
+        FB_CUDA(cudaMemcpyAsync(c->h_pinned, d_ob, 128, cudaMemcpyDeviceToHost, st));
+        int rc = ctx_check_err(c);
+        if (rc) return rc;
+        memcpy(out_z_be, c->h_pinned, 32);
+        memcpy(out_pi0_48, c->h_pinned + 32, 48);
+        memcpy(out_pi1_48, c->h_pinned + 80, 48);
+        return FB_OK;
+    });
+}
+
+// ------------------------------------------------------- device-resident calls
+int fb_dev_worker_commit(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, void* d_out48) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, i, 1);
+        if (rc) return rc;
+        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
+        G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
+        msm_run(row_bases(c, i), (const Fr*)d_coeffs, len, 1, true, d_r, c->msm, c->stream);
+        ctx_points_out(c, d_r, 1, (uint8_t*)d_out48);
+        return FB_OK;
+    });
+}
+
+int fb_dev_worker_open(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, const void* d_alpha, void* d_out80) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, i, 1);
+        if (rc) return rc;
+        int lg = ilog2_exact(len);
+        if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+        const NttTables& tab = ctx_ntt_tables(c, lg);
+        Fr* d_y = (Fr*)c->msm.misc.get(4 * sizeof(Fr));
+        Fr* d_qhat = open_scalars(c, tab, (const Fr*)d_coeffs, len, (const Fr*)d_alpha, d_y);
+        G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
+        msm_run(row_bases(c, i), d_qhat, len, 1, true, d_r, c->msm, c->stream);
+        fr_to_be(d_y, (uint8_t*)d_out80, 1, c->stream);
+        ctx_points_out(c, d_r, 1, (uint8_t*)d_out80 + 32);
+        return FB_OK;
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,294 @@
+// ntt.cu - Fr number-theoretic transform, natural order in and out.
+//
+// Replaces FsFFTSettings::fft_fr as called through PianoFFTSettings::fft_left /
+// fft_right (reference src/engine/piano.rs:1096-1103): out[k] = sum_j in[j] w^(jk)
+// with w = 7^((r-1)/N); the inverse uses w^-1 and scales by 1/N.
+//
+// Decomposition.  N = R1*R2*...*Rp (each Rj <= 2^10).  Pass j transforms the most
+// significant remaining input digit: the buffer is viewed as R rows by C = N/R
+// columns, a CTA owns all R rows of B adjacent columns (R*B elements staged in
+// shared memory, limb-plane layout), runs log2(R) radix-2 DIF stages there, then
+// multiplies element (k, c) by the inter-pass twiddle w_N^(k * (c/Q) * Q) and
+// scatters it to  (c/Q)*(R*Q) + k*Q + (c mod Q),  Q = R1*...*R(j-1).  After the
+// last pass the digits are fully reversed, i.e. the output is in natural order.
+// Global traffic per pass is one 32-byte read and one 32-byte write per element,
+// in segments of B*32 bytes (reads) and B*32 or R*32 bytes (writes).
+#include "common.cuh"
+
+namespace fb {
+
+namespace {
+
+__constant__ uint32_t kRoot32[2][8] = {
+    // 7^((r-1)/2^32) and its inverse, Montgomery form
+    {0x5f0e466au, 0xb9b58d8cu, 0x1819d7ecu, 0x5b1b4c80u, 0x52a31e64u, 0x0af53ae3u, 0x19e9b27bu, 0x5bf3addau},
+    {0xdcf3219au, 0x4256481au, 0x96b6cad3u, 0x45f37b7fu, 0x5f7a3b27u, 0xf9c3f1d7u, 0x658afd43u, 0x2d2fc049u}};
+
+__device__ __forceinline__ Fr fr_pow_u64(Fr base, uint64_t e) {
+    Fr r = Fr::one();
+    while (e) {
+        if (e & 1) r = fe_mul<FrParams>(r, base);
+        e >>= 1;
+        if (e) base = fe_sqr<FrParams>(base);
+    }
+    return r;
+}
+
+// consts[0] = w_N, consts[1] = w_N^-1, consts[2] = 1/N
+__global__ void k_ntt_consts(Fr* consts, int log_n) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    for (int d = 0; d < 2; d++) {
+        Fr w;
+        for (int i = 0; i < 8; i++) w.v[i] = kRoot32[d][i];
+        for (int i = log_n; i < 32; i++) w = fe_sqr<FrParams>(w);
+        consts[d] = w;
+    }
+    // 1/2 = (r+1)/2 -> Montgomery
+    Fr half = Fr::modulus();
+    // (r+1)/2: r is odd, so (r+1)/2 = (r>>1) + 1
+    for (int i = 0; i < 8; i++) half.v[i] = (half.v[i] >> 1) | (i < 7 ? (Fr::modulus().v[i + 1] << 31) : 0u);
+    half.v[0] += 1;  // r>>1 ends in ...0000 (r = ...00000001), no carry
+    half = fe_to_mont<FrParams>(half);
+    Fr ninv = Fr::one();
+    for (int i = 0; i < log_n; i++) ninv = fe_mul<FrParams>(ninv, half);
+    consts[2] = ninv;
+}
+
+// out[x] = base^(x << shift) [* scale]
+__global__ void k_pow_table(Fr* out, uint32_t count, const Fr* base, int shift, const Fr* scale) {
+    uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= count) return;
+    Fr r = fr_pow_u64(*base, (uint64_t)x << shift);
+    if (scale) r = fe_mul<FrParams>(r, *scale);
+    out[x] = r;
+}
+
+// tile twiddles: for every log_r in 1..10, w_R^j for j < R/2 at offset (R/2 - 1)
+__global__ void k_tile_twiddles(Fr* out, int dir) {
+    uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;  // 0 .. 1022
+    if (idx >= 1023) return;
+    int log_half = 31 - __clz(idx + 1);  // R/2 = 2^log_half
+    uint32_t j = idx + 1 - (1u << log_half);
+    int log_r = log_half + 1;
+    Fr w;
+    for (int i = 0; i < 8; i++) w.v[i] = kRoot32[dir][i];
+    for (int i = log_r; i < 32; i++) w = fe_sqr<FrParams>(w);
+    out[idx] = fr_pow_u64(w, j);
+}
+
+struct PassArgs {
+    const Fr* in;
+    Fr* out;
+    int log_r, log_b, log_q, lo_bits;
+    unsigned long long C;
+    int twiddle, scale;
+    const Fr* tw_lo;
+    const Fr* tw_hi;
+    const Fr* tile_tw;
+    const Fr* n_inv;
+};
+
+__device__ __forceinline__ Fr lds_fr(const uint4* p0, const uint4* p1, uint32_t e) {
+    Fr r;
+    uint4 a = p0[e], b = p1[e];
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+    r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+}
+__device__ __forceinline__ void sts_fr(uint4* p0, uint4* p1, uint32_t e, const Fr& r) {
+    p0[e] = make_uint4(r.v[0], r.v[1], r.v[2], r.v[3]);
+    p1[e] = make_uint4(r.v[4], r.v[5], r.v[6], r.v[7]);
+}
+__device__ __forceinline__ Fr ldg_fr(const Fr* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    Fr r;
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+    r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+}
+
+__global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
+    extern __shared__ uint4 smem[];
+    const uint32_t R = 1u << a.log_r, B = 1u << a.log_b;
+    const uint32_t tile = R << a.log_b;
+    uint4* s0 = smem;
+    uint4* s1 = smem + tile;
+    uint4* t0 = smem + 2 * tile;
+    uint4* t1 = t0 + (R >> 1);
+    const uint32_t tid = threadIdx.x, nt = blockDim.x;
+    const unsigned long long c0 = (unsigned long long)blockIdx.x << a.log_b;
+
+    for (uint32_t e = tid; e < tile; e += nt) {
+        uint32_t cb = e & (B - 1), r = e >> a.log_b;
+        const uint4* src = reinterpret_cast<const uint4*>(a.in + ((unsigned long long)r * a.C + c0 + cb));
+        s0[e] = src[0];
+        s1[e] = src[1];
+    }
+    for (uint32_t j = tid; j < (R >> 1); j += nt) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.tile_tw + j);
+        t0[j] = __ldg(src);
+        t1[j] = __ldg(src + 1);
+    }
+    __syncthreads();
+
+    // radix-2 decimation-in-frequency stages: natural in, bit-reversed out
+    for (int s = a.log_r - 1; s >= 0; s--) {
+        const uint32_t h = 1u << s;
+        for (uint32_t p = tid; p < (tile >> 1); p += nt) {
+            uint32_t cb = p & (B - 1), pr = p >> a.log_b;
+            uint32_t j = pr & (h - 1);
+            uint32_t i = ((pr >> s) << (s + 1)) | j;
+            uint32_t e0 = (i << a.log_b) | cb, e1 = e0 + (h << a.log_b);
+            Fr u = lds_fr(s0, s1, e0), v = lds_fr(s0, s1, e1);
+            Fr sum = fe_add<FrParams>(u, v);
+            Fr dif = fe_sub<FrParams>(u, v);
+            if (s > 0) dif = fe_mul<FrParams>(dif, lds_fr(t0, t1, j << (a.log_r - 1 - s)));
+            sts_fr(s0, s1, e0, sum);
+            sts_fr(s0, s1, e1, dif);
+        }
+        __syncthreads();
+    }
+
+    const uint32_t lo_mask = (1u << a.lo_bits) - 1;
+    const unsigned long long qmask = (1ull << a.log_q) - 1;
+    Fr ninv;
+    if (a.scale) ninv = *a.n_inv;
+    for (uint32_t e = tid; e < tile; e += nt) {
+        uint32_t k, cb;
+        if (a.log_q == 0) {  // transposing pass: rows are contiguous in the output
+            k = e & (R - 1);
+            cb = e >> a.log_r;
+        } else {
+            cb = e & (B - 1);
+            k = e >> a.log_b;
+        }
+        uint32_t pos = __brev(k) >> (32 - a.log_r);
+        if (a.log_r == 0) pos = 0;
+        Fr val = lds_fr(s0, s1, (pos << a.log_b) | cb);
+        unsigned long long c = c0 + cb;
+        unsigned long long rest = c >> a.log_q;
+        if (a.twiddle) {
+            unsigned long long x = ((unsigned long long)k * rest) << a.log_q;
+            Fr t = fe_mul<FrParams>(ldg_fr(a.tw_hi + (x >> a.lo_bits)), ldg_fr(a.tw_lo + (x & lo_mask)));
+            val = fe_mul<FrParams>(val, t);
+        }
+        if (a.scale) val = fe_mul<FrParams>(val, ninv);
+        unsigned long long o = (rest << (a.log_q + a.log_r)) | ((unsigned long long)k << a.log_q) | (c & qmask);
+        uint4* dst = reinterpret_cast<uint4*>(a.out + o);
+        dst[0] = make_uint4(val.v[0], val.v[1], val.v[2], val.v[3]);
+        dst[1] = make_uint4(val.v[4], val.v[5], val.v[6], val.v[7]);
+    }
+}
+
+constexpr int kTileLog = 11;  // elements staged per CTA = 2^11 (64 KiB of shared memory)
+
+}  // namespace
+
+NttPlan ntt_make_plan(int log_n) {
+    NttPlan p;
+    if (log_n <= 10) {
+        p.npass = 1;
+        p.log_r[0] = log_n;
+    } else if (log_n <= 20) {
+        p.npass = 2;
+        p.log_r[0] = (log_n + 1) / 2;
+        p.log_r[1] = log_n - p.log_r[0];
+    } else {
+        p.npass = 3;
+        p.log_r[0] = (log_n + 2) / 3;
+        p.log_r[1] = (log_n - p.log_r[0] + 1) / 2;
+        p.log_r[2] = log_n - p.log_r[0] - p.log_r[1];
+    }
+    return p;
+}
+
+void ntt_build_tile_twiddles(TileTwiddles& t, cudaStream_t st) {
+    for (int d = 0; d < 2; d++) {
+        FB_CUDA(cudaMalloc(&t.base[d], 1023 * sizeof(Fr)));
+        (++fb::g_launches, k_tile_twiddles<<<8, 128, 0, st>>>(t.base[d], d));
+    }
+    FB_CUDA(cudaGetLastError());
+}
+
+void ntt_build_tables(NttTables& t, int log_n, cudaStream_t st) {
+    t.log_n = log_n;
+    t.lo_bits = (log_n + 1) / 2;
+    int hi_bits = log_n - t.lo_bits;
+    uint32_t nlo = 1u << t.lo_bits, nhi = 1u << hi_bits;
+    Fr* consts;
+    FB_CUDA(cudaMalloc(&consts, 3 * sizeof(Fr)));
+    (++fb::g_launches, k_ntt_consts<<<1, 1, 0, st>>>(consts, log_n));
+    for (int d = 0; d < 2; d++) {
+        FB_CUDA(cudaMalloc(&t.lo[d], nlo * sizeof(Fr)));
+        FB_CUDA(cudaMalloc(&t.hi[d], nhi * sizeof(Fr)));
+        (++fb::g_launches, k_pow_table<<<(nlo + 127) / 128, 128, 0, st>>>(t.lo[d], nlo, consts + d, 0, nullptr));
+        (++fb::g_launches, k_pow_table<<<(nhi + 127) / 128, 128, 0, st>>>(t.hi[d], nhi, consts + d, t.lo_bits, d == 1 ? consts + 2 : nullptr));
+    }
+    FB_CUDA(cudaMalloc(&t.hi_unscaled_inv, nhi * sizeof(Fr)));
+    (++fb::g_launches, k_pow_table<<<(nhi + 127) / 128, 128, 0, st>>>(t.hi_unscaled_inv, nhi, consts + 1, t.lo_bits, nullptr));
+    t.consts = consts;
+    FB_CUDA(cudaGetLastError());
+}
+
+void ntt_free_tables(NttTables& t) {
+    for (int d = 0; d < 2; d++) {
+        if (t.lo[d]) cudaFree(t.lo[d]);
+        if (t.hi[d]) cudaFree(t.hi[d]);
+        t.lo[d] = t.hi[d] = nullptr;
+    }
+    if (t.hi_unscaled_inv) cudaFree(t.hi_unscaled_inv);
+    if (t.consts) cudaFree(t.consts);
+    t.hi_unscaled_inv = nullptr;
+    t.consts = nullptr;
+    t.log_n = -1;
+}
+
+void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out, Fr* scratch, bool inverse,
+             cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        attr_set = true;
+    }
+    const int log_n = tab.log_n;
+    const int d = inverse ? 1 : 0;
+    NttPlan plan = ntt_make_plan(log_n);
+    const Fr* src = in;
+    int log_q = 0;
+    for (int j = 0; j < plan.npass; j++) {
+        PassArgs a;
+        a.log_r = plan.log_r[j];
+        int log_c = log_n - a.log_r;
+        a.C = 1ull << log_c;
+        a.log_b = kTileLog - a.log_r;
+        if (a.log_b > log_c) a.log_b = log_c;
+        if (a.log_b > 3) a.log_b = 3;
+        a.log_q = log_q;
+        a.lo_bits = tab.lo_bits;
+        bool last = (j == plan.npass - 1);
+        a.twiddle = last ? 0 : 1;
+        a.scale = (inverse && plan.npass == 1) ? 1 : 0;
+        a.tw_lo = tab.lo[d];
+        // the inverse transform's 1/N rides on the first pass's twiddle table
+        a.tw_hi = inverse ? (j == 0 ? tab.hi[1] : tab.hi_unscaled_inv) : tab.hi[0];
+        a.tile_tw = a.log_r >= 1 ? tt.base[d] + ((1u << (a.log_r - 1)) - 1) : tt.base[d];
+        a.n_inv = tab.consts + 2;
+        a.in = src;
+        Fr* dst;
+        if (plan.npass == 1) dst = out;
+        else if (j == 0) dst = scratch;
+        else dst = out;
+        a.out = dst;
+        uint32_t tile = 1u << (a.log_r + a.log_b);
+        uint32_t threads = tile / 2 < 32 ? 32 : (tile / 2 > 512 ? 512 : tile / 2);
+        size_t smem = (size_t)tile * 32 + ((size_t)1 << a.log_r) * 16;
+        unsigned long long blocks = a.C >> a.log_b;
+        (++fb::g_launches, k_ntt_pass<<<(unsigned)blocks, threads, smem, st>>>(a));
+        src = dst;
+        log_q += a.log_r;
+    }
+    FB_CUDA(cudaGetLastError());
+}
+
+}  // namespace fb

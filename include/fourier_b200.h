@@ -1,0 +1,147 @@
+/* fourier_b200.h - C ABI of the B200-native KZG / Pianist hot path.
+ *
+ * Drop-in boundary for apollozkp/fourier's engine: every entry point below
+ * replaces one call the reference makes from src/engine/piano.rs into the
+ * rust-kzg-blst / blst crates (the file:line after "replaces").  A Rust `-sys`
+ * crate, cgo, JNI or ctypes binds these symbols directly: plain pointers and
+ * sizes, caller-allocated outputs, `int` status (0 = ok) with the message
+ * available from fb_last_error().
+ *
+ * Encodings at the boundary are the reference's wire encodings:
+ *   Fr  : 32 bytes big-endian, canonical (< r) else FB_ERR_SCALAR ("Invalid scalar")
+ *   G1  : 48 bytes ZCash-compressed (FsG1::to_bytes / from_bytes), or 96 bytes
+ *         uncompressed (FsG1::serialize / deserialize) where stated
+ * Montgomery limbs, affine/XYZZ points and window tables never leave the library.
+ *
+ * A context is bound to ONE CUDA device (one process per GPU); it owns the SRS,
+ * the window tables, the twiddle tables and all scratch memory in HBM.  Calls on
+ * one context are serialised by an internal mutex, so concurrent callers (the
+ * reference runs one tokio task per connection, src/rpc.rs:502) are safe.
+ * There is no CPU fallback: without a usable CUDA device fb_ctx_create fails.
+ */
+#ifndef FOURIER_B200_H
+#define FOURIER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fb_ctx fb_ctx;
+
+enum {
+    FB_OK = 0,
+    FB_ERR_CUDA = 1,     /* CUDA runtime / launch failure */
+    FB_ERR_ARG = 2,      /* bad argument (row index, length not a power of two, ...) */
+    FB_ERR_SCALAR = 3,   /* "Invalid scalar": an Fr encoding >= r */
+    FB_ERR_POINT = 4,    /* a G1 encoding that does not decode to a curve point */
+    FB_ERR_STATE = 5,    /* SRS not loaded / wrong shard */
+    FB_ERR_IO = 6        /* file errors */
+};
+
+/* ---- context -------------------------------------------------------------
+ * replaces PianoBackend::new + PianoFFTSettings::new (piano.rs:82-85, 1061-1077):
+ * scale n (total 2^n coefficients), machines_scale m (2^m rows of 2^(n-m)).
+ * `device` is the CUDA ordinal.  Fails with FB_ERR_ARG if m > n. */
+int fb_ctx_create(uint32_t n, uint32_t m, int device, fb_ctx** out);
+void fb_ctx_destroy(fb_ctx* ctx);
+const char* fb_last_error(const fb_ctx* ctx); /* message of the last failing call on ctx */
+const char* fb_version(void);
+/* run all work of this context on an existing CUDA stream (cudaStream_t passed as
+ * void*), e.g. torch's current stream; NULL restores the context's own stream */
+int fb_ctx_set_stream(fb_ctx* ctx, void* cuda_stream);
+int fb_ctx_sync(fb_ctx* ctx);
+/* window bits for the resident tables built by the next SRS load/generate
+ * (0 = pick from the row length; -1 = no tables: plain Pippenger per call) */
+int fb_ctx_set_window(fb_ctx* ctx, int window_bits);
+
+/* ---- SRS -------------------------------------------------------------------
+ * Rows [row0, row0+nrows) of U are kept resident on this context's device
+ * (nrows = 0 means all 2^m rows).  Sharding rows over GPUs = one context per GPU
+ * with disjoint row ranges.
+ *
+ * fb_srs_generate replaces generate_trusted_setup (piano.rs:883-1037): tau_X,
+ * tau_Y = the 32-byte secrets read big-endian mod r; U[i][j] = g^(R_i(tau_Y) *
+ * L_j(tau_X)), g_tau_y[k] = g^(tau_Y^k).  Lagrange values use the closed form
+ * (identical field elements to the reference's iFFT + Horner). */
+int fb_srs_generate(fb_ctx* ctx, const uint8_t secret_x[32], const uint8_t secret_y[32], uint64_t row0,
+                    uint64_t nrows);
+/* replaces PianoSettings::load_setup_from_file (piano.rs:711-846); G1 points are
+ * decoded on the GPU.  compressed != 0: 48/96-byte elements, else 96/192. */
+int fb_srs_load_file(fb_ctx* ctx, const char* path, int compressed, uint64_t row0, uint64_t nrows);
+int fb_srs_load_bytes(fb_ctx* ctx, const uint8_t* buf, size_t len, int compressed, uint64_t row0, uint64_t nrows);
+/* replaces PianoSettings::save_setup_to_file (piano.rs:649-706); needs all rows resident */
+int fb_srs_save_file(fb_ctx* ctx, const char* path, int compressed);
+/* size of / copy of the serialised setup (same layout as the file) */
+int fb_srs_to_bytes(fb_ctx* ctx, int compressed, uint8_t* out, size_t cap, size_t* written);
+
+/* ---- engine: worker side -----------------------------------------------------
+ * fb_worker_commit replaces PianoBackend::worker_commit (piano.rs:143-161):
+ * out = sum_j coeffs[j] * U[i][j].  len <= 2^(n-m). */
+int fb_worker_commit(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, uint8_t out48[48]);
+/* replaces PianoBackend::worker_open (piano.rs:187-238): p = iNTT(coeffs),
+ * y = p(alpha), q = (p - y)/(X - alpha), proof = sum_j NTT(q||0)[j] * U[i][j]. */
+int fb_worker_open(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                   uint8_t out_y_be[32], uint8_t out_proof48[48]);
+/* batched rows [row0, row0+nrows): coeffs is nrows*len Fr, outputs nrows entries */
+int fb_commit_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len,
+                   uint8_t* out48s);
+int fb_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len,
+                 const uint8_t alpha_be[32], uint8_t* out_ys_be, uint8_t* out_proof48s);
+
+/* ---- engine: master side ------------------------------------------------------
+ * replaces PianoBackend::master_commit (piano.rs:164-175): sum of the commitments */
+int fb_master_commit(fb_ctx* ctx, const uint8_t* commitments48, uint64_t count, uint8_t out48[48]);
+/* replaces PianoBackend::master_open (piano.rs:250-298) */
+int fb_master_open(fb_ctx* ctx, const uint8_t* evals_be, const uint8_t* proofs48, uint64_t count,
+                   const uint8_t beta_be[32], uint8_t out_z_be[32], uint8_t out_pi0_48[48], uint8_t out_pi1_48[48]);
+
+/* ---- field-side RPC helpers -----------------------------------------------------
+ * replaces PianoFFTSettings::fft_left / fft_right (piano.rs:1096-1103) as exposed
+ * by the `fft` RPC (src/rpc.rs:66-70): left != 0 uses the 2^(n-m) domain. */
+int fb_fft(fb_ctx* ctx, int left, int inverse, const uint8_t* in_be, uint64_t len, uint8_t* out_be);
+/* replaces FsPoly::eval as exposed by the `evaluate` RPC (src/rpc.rs:60-64) */
+int fb_evaluate(fb_ctx* ctx, const uint8_t* poly_be, uint64_t len, const uint8_t x_be[32], uint8_t out_y_be[32]);
+
+/* ---- raw kernels (benches, sharded MSM) ------------------------------------------
+ * A base set is an array of G1 points resident on the device, optionally with
+ * window tables.  format: 48 = compressed, 96 = uncompressed. */
+typedef struct fb_bases fb_bases;
+int fb_bases_from_points(fb_ctx* ctx, const uint8_t* points, uint64_t count, int format, fb_bases** out);
+/* P_k = s_k * G for the given scalars (synthetic bases with known discrete logs) */
+int fb_bases_from_scalars(fb_ctx* ctx, const uint8_t* scalars_be, uint64_t count, fb_bases** out);
+int fb_bases_precompute(fb_ctx* ctx, fb_bases* b, int window_bits);
+int fb_bases_get(fb_ctx* ctx, const fb_bases* b, uint64_t index, uint8_t out48[48]);
+void fb_bases_free(fb_ctx* ctx, fb_bases* b);
+/* replaces g1_linear_combination on arbitrary points: out = sum_k s_k * P_k */
+int fb_msm(fb_ctx* ctx, const fb_bases* b, const uint8_t* scalars_be, uint64_t count, uint8_t out48[48]);
+/* same, result left uncompressed (96 bytes) so partial sums of a sharded MSM can
+ * be combined with fb_g1_sum */
+int fb_msm_partial(fb_ctx* ctx, const fb_bases* b, const uint8_t* scalars_be, uint64_t count, uint8_t out96[96]);
+int fb_g1_sum(fb_ctx* ctx, const uint8_t* points, uint64_t count, int format, uint8_t out48[48]);
+/* NTT of any power-of-two length (tables cached per size) */
+int fb_ntt(fb_ctx* ctx, int inverse, const uint8_t* in_be, uint64_t len, uint8_t* out_be);
+
+/* ---- device-resident entry points ----------------------------------------------------
+ * Same kernels, operands already in HBM (device pointers, e.g. torch tensors):
+ * Fr vectors are arrays of 32-byte Montgomery elements as produced by
+ * fb_dev_fr_from_be.  Asynchronous on the context's stream. */
+int fb_dev_fr_from_be(fb_ctx* ctx, const void* d_in_be, void* d_out_fr, uint64_t count);
+int fb_dev_fr_to_be(fb_ctx* ctx, const void* d_in_fr, void* d_out_be, uint64_t count);
+int fb_dev_ntt(fb_ctx* ctx, int inverse, const void* d_in_fr, void* d_out_fr, uint64_t len);
+/* d_out: 48 bytes (device) */
+int fb_dev_msm(fb_ctx* ctx, const fb_bases* b, const void* d_scalars_fr, uint64_t count, void* d_out48);
+int fb_dev_worker_commit(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, void* d_out48);
+/* d_out: 32 bytes y (big-endian) followed by 48 bytes proof */
+int fb_dev_worker_open(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
+                       void* d_out80);
+
+/* number of kernel launches issued by this context so far */
+uint64_t fb_launch_count(const fb_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FOURIER_B200_H */
