@@ -2,7 +2,7 @@
 # host-arithmetic test harness.  `python __graft_entry__.py build` runs this.
 NVCC      ?= nvcc
 CXX       ?= g++
-CC        ?= gcc
+CC        := /usr/bin/gcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2 --expt-relaxed-constexpr -Xptxas -v
 CSRC      := fourier_b200/csrc

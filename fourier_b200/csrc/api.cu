@@ -8,6 +8,7 @@
 namespace fb {
 
 unsigned long long g_launches = 0;
+thread_local Prof* g_prof = nullptr;
 
 int ctx_fail(fb_ctx* c, int code, const std::string& msg) {
     c->err = msg;
@@ -33,6 +34,7 @@ Fr* ctx_upload_fr(fb_ctx* c, DevBuf& bytes, DevBuf& dst, const uint8_t* h_be, si
     uint8_t* d_b = bytes.as<uint8_t>(count * 32 + 32);
     Fr* d = dst.as<Fr>(count + 1);
     if (count) {
+        prof_mark("h2d", c->stream);
         FB_CUDA(cudaMemcpyAsync(d_b, h_be, count * 32, cudaMemcpyHostToDevice, c->stream));
         fr_from_be(d_b, d, count, c->d_err, c->stream);
     }
@@ -54,6 +56,7 @@ int ctx_check_err(fb_ctx* c) {
 // XYZZ results -> 48-byte compressed strings on the device
 void ctx_points_out(fb_ctx* c, const G1Xyzz* d_xyzz, size_t count, uint8_t* d_out48) {
     G1Affine* aff = c->pt_b.as<G1Affine>(count + 1);
+    prof_mark("out.affine_compress", c->stream);
     g1_xyzz_to_affine_batch(d_xyzz, aff, count, c->stream);
     g1_compress_batch(aff, d_out48, count, c->stream);
 }
@@ -141,6 +144,46 @@ int fb_ctx_set_window(fb_ctx* c, int w) {
 }
 
 uint64_t fb_launch_count(const fb_ctx*) { return g_launches; }
+
+int fb_prof_enable(fb_ctx* c, int on) {
+    if (!c) return FB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->prof.on = on != 0;
+    return FB_OK;
+}
+
+// JSON object {"phase": [total_ms, count], ...} of everything marked since the last read
+int fb_prof_read(fb_ctx* c, char* buf, size_t cap) {
+    if (!c || !buf || cap < 3) return FB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    std::map<std::string, std::pair<double, int>> acc;
+    auto& m = c->prof.marks;
+    for (size_t i = 0; i + 1 < m.size(); i++) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, m[i].second, m[i + 1].second) != cudaSuccess) ms = 0;
+        auto& a = acc[m[i].first];
+        a.first += ms;
+        a.second += 1;
+    }
+    for (auto& kv : m) c->prof.pool.push_back(kv.second);
+    m.clear();
+    cudaGetLastError();
+    std::string out = "{";
+    bool first = true;
+    for (auto& kv : acc) {
+        if (kv.first == "idle") continue;
+        char tmp[160];
+        snprintf(tmp, sizeof tmp, "%s\"%s\": [%.6f, %d]", first ? "" : ", ", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += tmp;
+        first = false;
+    }
+    out += "}";
+    if (out.size() + 1 > cap) return FB_ERR_ARG;
+    memcpy(buf, out.c_str(), out.size() + 1);
+    return FB_OK;
+}
 
 // ------------------------------------------------------------ field-side calls
 static int do_ntt_host(fb_ctx* c, int log_n, bool inverse, const uint8_t* in_be, uint64_t len, uint8_t* out_be) {

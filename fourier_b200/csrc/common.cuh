@@ -31,6 +31,29 @@ struct CudaError {
         }                                                                                               \
     } while (0)
 
+// Optional per-phase timing with CUDA events on the launching stream (bench.py's
+// roofline numbers).  prof_mark(name) says "phase `name` starts here"; the time to
+// the next mark is charged to it.  A no-op unless enabled through fb_prof_enable.
+struct Prof {
+    bool on = false;
+    std::vector<std::pair<const char*, cudaEvent_t>> marks;
+    std::vector<cudaEvent_t> pool;
+};
+extern thread_local Prof* g_prof;
+inline void prof_mark(const char* name, cudaStream_t st) {
+    Prof* p = g_prof;
+    if (!p || !p->on) return;
+    cudaEvent_t e;
+    if (!p->pool.empty()) {
+        e = p->pool.back();
+        p->pool.pop_back();
+    } else {
+        cudaEventCreate(&e);
+    }
+    cudaEventRecord(e, st);
+    p->marks.emplace_back(name, e);
+}
+
 // grow-only device scratch buffer
 struct DevBuf {
     void* p = nullptr;

@@ -39,6 +39,7 @@ struct fb_ctx {
     // scratch
     fb::MsmScratch msm;
     fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small;
+    fb::Prof prof;
     int* d_err = nullptr;
     uint8_t* h_pinned = nullptr;  // small pinned result buffer
     size_t h_pinned_cap = 0;
@@ -51,7 +52,14 @@ extern unsigned long long g_launches;
 struct CtxGuard {
     fb_ctx* c;
     std::unique_lock<std::mutex> lk;
-    explicit CtxGuard(fb_ctx* ctx) : c(ctx), lk(ctx->mu) { cudaSetDevice(ctx->device); }
+    explicit CtxGuard(fb_ctx* ctx) : c(ctx), lk(ctx->mu) {
+        cudaSetDevice(ctx->device);
+        g_prof = &ctx->prof;
+    }
+    ~CtxGuard() {
+        prof_mark("idle", c->stream);
+        g_prof = nullptr;
+    }
 };
 
 const NttTables& ctx_ntt_tables(fb_ctx* c, int log_n);

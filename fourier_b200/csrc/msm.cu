@@ -306,6 +306,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     uint32_t* sorted = s.sorted.as<uint32_t>((size_t)n * nwin);
     G1Xyzz* buckets = s.buckets.as<G1Xyzz>(nbuckets);
 
+    prof_mark("msm.digits_count", st);
     FB_CUDA(cudaMemsetAsync(counts, 0, nbuckets * sizeof(uint32_t), st));
     DigitArgs a;
     a.scalars = d_scalars;
@@ -322,13 +323,17 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     DigitArgs a2 = a;
     const unsigned gb = (unsigned)((n + 255) / 256);
     (++fb::g_launches, k_digits<false><<<gb, 256, 0, st>>>(a));
+    prof_mark("msm.scan", st);
     exclusive_scan(counts, offsets, nbuckets, s.block_sums, st);
     FB_CUDA(cudaMemcpyAsync(cursor, offsets, nbuckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     a2.counts = cursor;
+    prof_mark("msm.scatter", st);
     (++fb::g_launches, k_digits<true><<<gb, 256, 0, st>>>(a2));
+    prof_mark("msm.accumulate", st);
     (++fb::g_launches, k_accumulate<<<(nbuckets + 127) / 128, 128, 0, st>>>(bases.pts, sorted, offsets, cursor, nbuckets, buckets));
 
     // bucket reduction
+    prof_mark("msm.reduce", st);
     const G1Xyzz* X = buckets;
     const G1Xyzz* P = nullptr;
     uint32_t m = bpw_pad;
@@ -345,7 +350,9 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         P = Po;
         m = mo;
     }
+    prof_mark("msm.finish", st);
     (++fb::g_launches, k_finish<<<(unsigned)batch, 64, 0, st>>>(X, P, m, per_out, c, d_out));
+    prof_mark("post", st);
     FB_CUDA(cudaGetLastError());
 }
 

@@ -284,10 +284,13 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         uint32_t threads = tile / 2 < 32 ? 32 : (tile / 2 > 512 ? 512 : tile / 2);
         size_t smem = (size_t)tile * 32 + ((size_t)1 << a.log_r) * 16;
         unsigned long long blocks = a.C >> a.log_b;
+        static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
+        prof_mark(names[j], st);
         (++fb::g_launches, k_ntt_pass<<<(unsigned)blocks, threads, smem, st>>>(a));
         src = dst;
         log_q += a.log_r;
     }
+    prof_mark("post", st);
     FB_CUDA(cudaGetLastError());
 }
 

@@ -124,11 +124,13 @@ __global__ void k_horner_down(const Fr* __restrict__ a, size_t n, const Fr* beta
 
 void fr_from_be(const uint8_t* d_in, Fr* d_out, size_t n, int* d_err, cudaStream_t st) {
     if (!n) return;
+    prof_mark("codec.fr_from_be", st);
     (++fb::g_launches, k_fr_from_be<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_in, d_out, n, d_err));
     FB_CUDA(cudaGetLastError());
 }
 void fr_to_be(const Fr* d_in, uint8_t* d_out, size_t n, cudaStream_t st) {
     if (!n) return;
+    prof_mark("codec.fr_to_be", st);
     (++fb::g_launches, k_fr_to_be<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_in, d_out, n));
     FB_CUDA(cudaGetLastError());
 }
@@ -144,6 +146,7 @@ void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, D
         FB_CUDA(cudaMemsetAsync(d_y, 0, sizeof(Fr), st));
         return;
     }
+    prof_mark("poly.scan", st);
     // level sizes
     std::vector<size_t> sz{n};
     while (sz.back() > (size_t)kChunk) sz.push_back((sz.back() + kChunk - 1) >> kChunkLog);

@@ -138,8 +138,12 @@ int fb_dev_worker_commit(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint6
 int fb_dev_worker_open(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
                        void* d_out80);
 
-/* number of kernel launches issued by this context so far */
+/* number of kernel launches issued by this library so far */
 uint64_t fb_launch_count(const fb_ctx* ctx);
+/* per-phase device timing (CUDA events on the launching stream); fb_prof_read
+ * writes a JSON object {"phase": [total_ms, count], ...} and resets the log */
+int fb_prof_enable(fb_ctx* ctx, int on);
+int fb_prof_read(fb_ctx* ctx, char* buf, size_t cap);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,192 @@
+"""GPU parity: the PianoBackend protocol (setup, worker/master commit + open, setup
+file round trip) against the oracle's restatement of src/engine/piano.rs, bit-exact
+on the reference's wire encodings.  Follows the reference's own end-to-end tests
+(piano.rs:1414-1459 manual_commit_test, :1604-1722 pianist_test, :1789-1833
+test_save_and_load_setup, :1392-1412 identity inputs)."""
+import random
+
+import pytest
+
+from util import R, SECRET_X, SECRET_Y, bls, fr_list_to_bytes, opiano
+
+pytestmark = pytest.mark.gpu
+
+
+def make(n, m, window_bits=0):
+    from fourier_b200 import PianoBackend
+    b = PianoBackend(n, m, window_bits=window_bits)
+    b.setup(SECRET_X, SECRET_Y)
+    o = opiano.PianoOracle(n, m)
+    o.generate_trusted_setup(SECRET_X, SECRET_Y, with_points=(n <= 6))
+    return b, o
+
+
+@pytest.fixture(scope="module")
+def small(gpu):
+    b, o = make(5, 2)
+    yield b, o
+    b.close()
+
+
+def test_setup_bytes_match_oracle(small):
+    b, o = small
+    for compressed in (True, False):
+        assert b.setup_to_bytes(compressed) == opiano.setup_to_bytes(o.settings, compressed)
+
+
+def test_worker_commit_open_match_oracle(small):
+    b, o = small
+    rng = random.Random(9)
+    for i in range(o.M):
+        coeffs = [rng.randrange(R) for _ in range(o.T)]
+        alpha = rng.randrange(R)
+        c = b.worker_commit(i, coeffs)
+        assert c == bls.g1_compress(o.worker_commit(i, coeffs))
+        y, pi = b.worker_open(i, coeffs, alpha)
+        oy, opi = o.worker_open(i, coeffs, alpha)
+        assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
+        if i == 0:  # pairing check (slow in the oracle): one row is enough
+            assert o.worker_verify(i, bls.g1_decompress(c), alpha, oy, bls.g1_decompress(pi))
+
+
+def test_full_protocol_and_master_verify(small):
+    b, o = small
+    rng = random.Random(10)
+    rows = [[rng.randrange(R) for _ in range(o.T)] for _ in range(o.M)]
+    alpha, beta = rng.randrange(R), rng.randrange(R)
+    flat = [x for row in rows for x in row]
+    commits = b.commit_rows(0, o.M, flat)
+    assert commits == [b.worker_commit(i, rows[i]) for i in range(o.M)]
+    ys, pis = b.open_rows(0, o.M, flat, alpha)
+    com = b.master_commit(commits)
+    z, (pi0, pi1) = b.master_open(ys, pis, beta)
+    oc = o.master_commit([o.worker_commit(i, rows[i]) for i in range(o.M)])
+    opens = [o.worker_open(i, rows[i], alpha) for i in range(o.M)]
+    oz, (opi0, opi1) = o.master_open([y for y, _ in opens], [p for _, p in opens], beta)
+    assert com == bls.g1_compress(oc)
+    assert z == oz.to_bytes(32, "big")
+    assert pi0 == bls.g1_compress(opi0) and pi1 == bls.g1_compress(opi1)
+    # z == f(beta, alpha) (piano.rs:1478-1563) and the pairing equation holds
+    polys = [o.fft_left(r, True) for r in rows]
+    lag = [o.right_lagrange_poly(i) for i in range(o.M)]
+    want = sum(opiano.poly_eval(lag[i], beta) * opiano.poly_eval(polys[i], alpha) for i in range(o.M)) % R
+    assert oz == want
+    assert o.master_verify(bls.g1_decompress(com), beta, alpha, oz, (bls.g1_decompress(pi0), bls.g1_decompress(pi1)))
+    assert not o.master_verify(bls.g1_decompress(com), beta, alpha, (oz + 1) % R,
+                               (bls.g1_decompress(pi0), bls.g1_decompress(pi1)))
+
+
+def test_identity_and_degenerate_inputs(small):
+    b, o = small
+    ident = bls.g1_compress(bls.G1_INF)
+    zero = [0] * o.T
+    assert b.worker_commit(1, zero) == ident
+    y, pi = b.worker_open(1, zero, 5)
+    assert y == bytes(32) and pi == ident
+    ones = [1] * o.T  # constant evaluations -> constant polynomial, zero quotient
+    y, pi = b.worker_open(2, ones, 123456789)
+    assert y == (1).to_bytes(32, "big") and pi == ident
+    assert b.master_commit([ident] * o.M) == ident
+    z, (p0, p1) = b.master_open([0] * o.M, [ident] * o.M, 7)
+    assert z == bytes(32) and p0 == ident and p1 == ident
+    # alpha on the evaluation domain
+    w = bls.root_of_unity(o.t)
+    rng = random.Random(4)
+    coeffs = [rng.randrange(R) for _ in range(o.T)]
+    y, pi = b.worker_open(0, coeffs, w)
+    oy, opi = o.worker_open(0, coeffs, w)
+    assert y == oy.to_bytes(32, "big") == coeffs[1].to_bytes(32, "big") and pi == bls.g1_compress(opi)
+
+
+def test_errors(small):
+    from fourier_b200 import FourierError
+    b, o = small
+    with pytest.raises(FourierError):
+        b.worker_commit(o.M, [1] * o.T)  # i >= M
+    with pytest.raises(FourierError):
+        b.worker_open(0, [1] * 3, 1)  # not a power of two
+    with pytest.raises(FourierError) as ei:
+        b.worker_commit(0, [R] + [0] * (o.T - 1))
+    assert "Invalid scalar" in str(ei.value)
+    with pytest.raises(FourierError):
+        PianoBackendBad()
+
+
+def PianoBackendBad():
+    from fourier_b200 import PianoBackend
+    return PianoBackend(2, 3)  # m > n (piano.rs:1062-1064)
+
+
+def test_setup_file_roundtrip(small, tmp_path):
+    from fourier_b200 import PianoBackend
+    b, o = small
+    rng = random.Random(2)
+    coeffs = [rng.randrange(R) for _ in range(o.T)]
+    for compressed in (True, False):
+        p = str(tmp_path / ("setup_%d" % compressed))
+        b.save_setup_to_file(p, compressed)
+        b2 = PianoBackend(o.n, o.m)
+        b2.load_setup_from_file(p, compressed)
+        assert b2.setup_to_bytes(True) == b.setup_to_bytes(True)
+        assert b2.worker_commit(3, coeffs) == b.worker_commit(3, coeffs)
+        # a row shard only holds its rows
+        b3 = PianoBackend(o.n, o.m)
+        b3.load_setup_from_file(p, compressed, row0=2, nrows=1)
+        assert b3.worker_commit(2, coeffs) == b.worker_commit(2, coeffs)
+        from fourier_b200 import FourierError
+        with pytest.raises(FourierError):
+            b3.worker_commit(0, coeffs)
+        b2.close()
+        b3.close()
+    # an oracle-written file loads too
+    blob = opiano.setup_to_bytes(o.settings, True)
+    b4 = PianoBackend(o.n, o.m)
+    b4.load_setup_from_bytes(blob, True)
+    assert b4.worker_commit(1, coeffs) == bls.g1_compress(o.worker_commit(1, coeffs))
+    b4.close()
+
+
+def test_tau_zero_setup(gpu):
+    # test_piano_setup uses the all-zero secret (piano.rs:1461-1476): tau = 0
+    from fourier_b200 import PianoBackend
+    b = PianoBackend(4, 1)
+    b.setup(bytes(32), bytes(32))
+    o = opiano.PianoOracle(4, 1)
+    o.generate_trusted_setup(bytes(32), bytes(32))
+    assert b.setup_to_bytes(True) == opiano.setup_to_bytes(o.settings, True)
+    rng = random.Random(8)
+    coeffs = [rng.randrange(R) for _ in range(o.T)]
+    assert b.worker_commit(1, coeffs) == bls.g1_compress(o.worker_commit(1, coeffs))
+    y, pi = b.worker_open(1, coeffs, 3)
+    oy, opi = o.worker_open(1, coeffs, 3)
+    assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
+    b.close()
+
+
+@pytest.mark.parametrize("n,m,wb", [(12, 0, 0), (12, 0, -1), (14, 4, 0), (16, 0, 0)])
+def test_known_tau_commit_open(gpu, n, m, wb):
+    """Sizes where the oracle cannot afford the SRS points: C = G*(R_i * sum c_j L_j)."""
+    b, o = make(n, m, window_bits=wb)
+    rng = random.Random(n * 31 + m)
+    for i in sorted({0, o.M - 1, o.M // 2}):
+        coeffs = [rng.randrange(R) for _ in range(o.T)]
+        alpha = rng.randrange(R)
+        assert b.worker_commit(i, coeffs) == bls.g1_compress(o.worker_commit_known_tau(i, coeffs))
+        y, pi = b.worker_open(i, coeffs, alpha)
+        oy, opi = o.worker_open_known_tau(i, coeffs, alpha)
+        assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
+    b.close()
+
+
+def test_c2_degree_2_20_known_tau(gpu):
+    """BASELINE config 2: commit + open of a degree-2^20 polynomial, bit-exact."""
+    from fourier_b200 import synth
+    b, o = make(20, 0)
+    coeffs_b = synth.fr_bytes(31, o.T)
+    coeffs = synth.fr_ints(31, o.T)
+    alpha = synth.fr_ints(33, 1)[0]
+    assert b.worker_commit(0, coeffs_b) == bls.g1_compress(o.worker_commit_known_tau(0, coeffs))
+    y, pi = b.worker_open(0, coeffs_b, alpha)
+    oy, opi = o.worker_open_known_tau(0, coeffs, alpha)
+    assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
+    b.close()

@@ -1,0 +1,127 @@
+"""GPU parity: G1 MSM and point utilities against the oracle (bit-exact compressed
+bytes).  The reference pins MSM == naive sum (src/engine/piano.rs:1414-1459); the
+golden G1 bytes it lacks are pinned through known discrete logs:
+P_k = s_k*G  =>  sum k_k P_k = G * (sum k_k s_k mod r)   (SURVEY.md §8c)."""
+import random
+
+import pytest
+
+from util import R, bls, fr_list_to_bytes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def be(gpu):
+    from fourier_b200 import PianoBackend
+    b = PianoBackend(4, 0)
+    yield b
+    b.close()
+
+
+def expect(ss, ks):
+    return bls.g1_compress(bls.g1_mul(bls.G1_GEN, sum(s * k for s, k in zip(ss, ks)) % R))
+
+
+def test_fixed_base_points_match_oracle(be):
+    rng = random.Random(1)
+    ss = [0, 1, 2, R - 1, 255, 256, 1 << 128] + [rng.randrange(R) for _ in range(20)]
+    bases = be.bases_from_scalars(ss)
+    for i, s in enumerate(ss):
+        assert bases.point(i) == bls.g1_compress(bls.g1_mul(bls.G1_GEN, s)), i
+
+
+@pytest.mark.parametrize("n", [1, 2, 7, 8, 33, 100, 1000, 5000])
+@pytest.mark.parametrize("tab", [False, True])
+def test_msm_known_dlog(be, n, tab):
+    rng = random.Random(n * 2 + tab)
+    ss = [rng.randrange(R) for _ in range(n)]
+    ks = [rng.randrange(R) for _ in range(n)]
+    bases = be.bases_from_scalars(ss)
+    if tab:
+        bases.precompute()
+    assert be.msm(bases, ks) == expect(ss, ks)
+    # fewer scalars than bases
+    if n > 3:
+        assert be.msm(bases, ks[: n - 3]) == expect(ss, ks[: n - 3])
+
+
+@pytest.mark.parametrize("tab,c", [(False, 0), (True, 0), (True, 5), (True, 13)])
+def test_msm_edge_scalars_and_points(be, tab, c):
+    rng = random.Random(77)
+    n = 64
+    # duplicate points, P and -P, the identity, small and extreme scalars
+    ss = [rng.randrange(R) for _ in range(n)]
+    ss[1] = ss[0]
+    ss[2] = (R - ss[0]) % R
+    ss[3] = 0  # identity point
+    ss[4] = 1
+    ks = [rng.randrange(R) for _ in range(n)]
+    ks[0] = ks[1] = ks[2] = 5  # same bucket: P + P then + (-P)
+    ks[5] = 0
+    ks[6] = R - 1
+    ks[7] = 1
+    ks[8] = (1 << 255) % R
+    ks[9] = (1 << 254) - 1
+    bases = be.bases_from_scalars(ss)
+    if tab:
+        bases.precompute(c)
+    assert be.msm(bases, ks) == expect(ss, ks)
+    assert be.msm(bases, [0] * n) == bls.g1_compress(bls.G1_INF)
+    assert be.msm(bases, [1] * n) == expect(ss, [1] * n)
+    assert be.msm(bases, [R - 1] * n) == expect(ss, [R - 1] * n)
+    same = [12345] * n  # every point lands in one bucket
+    assert be.msm(bases, same) == expect(ss, same)
+
+
+def test_msm_from_compressed_points_and_sum(be):
+    rng = random.Random(3)
+    ss = [rng.randrange(R) for _ in range(40)] + [0]
+    pts = [bls.g1_compress(bls.g1_mul(bls.G1_GEN, s)) for s in ss]
+    ks = [rng.randrange(R) for _ in ss]
+    bases = be.bases_from_points(pts, 48)
+    assert be.msm(bases, ks) == expect(ss, ks)
+    ser = [bls.g1_serialize(bls.g1_mul(bls.G1_GEN, s)) for s in ss]
+    bases96 = be.bases_from_points(ser, 96)
+    assert be.msm(bases96, ks) == expect(ss, ks)
+    # point sums (master_commit, piano.rs:164-175), identity inputs included
+    assert be.g1_sum(pts) == expect(ss, [1] * len(ss))
+    assert be.master_commit(pts) == expect(ss, [1] * len(ss))
+    assert be.g1_sum([pts[0]]) == pts[0]
+    assert be.g1_sum([]) == bls.g1_compress(bls.G1_INF)
+    ident = bls.g1_compress(bls.G1_INF)
+    assert be.g1_sum([ident, ident]) == ident
+    # partial (uncompressed) results recombine: sharded MSM
+    a = be.msm_partial(bases, ks)
+    assert a == bls.g1_serialize(bls.g1_decompress(expect(ss, ks)))
+    assert be.g1_sum([a, a], fmt=96) == expect(ss, [2 * k for k in ks])
+
+
+def test_bad_point_rejected(be):
+    from fourier_b200 import FourierError
+    bad = bytes([0x80]) + bytes(46) + bytes([5])  # x = 5: x^3+4 = 129 is a non-residue? checked by the oracle
+    try:
+        bls.g1_decompress(bad)
+        pytest.skip("x=5 happens to be on the curve")
+    except ValueError:
+        pass
+    with pytest.raises(FourierError):
+        be.bases_from_points([bad], 48)
+    with pytest.raises(FourierError):
+        be.bases_from_points([bytes(48)], 48)  # compression bit missing
+
+
+@pytest.mark.parametrize("log_n,tab", [(16, False), (16, True), (20, True)])
+def test_msm_large_known_dlog(be, log_n, tab):
+    from fourier_b200 import synth
+    n = 1 << log_n
+    sb = synth.fr_bytes(21, n)
+    kb = synth.fr_bytes(22, n)
+    bases = be.bases_from_scalars(sb)
+    if tab:
+        bases.precompute()
+    got = be.msm(bases, kb)
+    ss = synth.fr_ints(21, n)
+    ks = synth.fr_ints(22, n)
+    assert got == expect(ss, ks)
+    bases.free()
