@@ -27,6 +27,8 @@ struct fb_ctx {
     // SRS (device, affine Montgomery)
     bool srs_ready = false;
     uint64_t row0 = 0, nrows = 0;
+    uint64_t col0 = 0, ncols = 0;      // resident column range of every row (ncols == T: whole rows)
+    uint64_t want_col0 = 0, want_ncols = 0;  // requested through fb_ctx_set_col_shard (0,0 = all)
     fb::G1Affine g;                    // host copy of the generator element of the setup
     fb::G1Affine* d_g_tau_x = nullptr; // [T]
     fb::G1Affine* d_g_tau_y = nullptr; // [M]
@@ -38,7 +40,7 @@ struct fb_ctx {
 
     // scratch
     fb::MsmScratch msm;
-    fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small;
+    fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small, eng_a, eng_b;
     fb::Prof prof;
     int* d_err = nullptr;
     uint8_t* h_pinned = nullptr;  // small pinned result buffer

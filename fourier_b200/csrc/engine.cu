@@ -35,18 +35,18 @@ void srs_free(fb_ctx* c) {
 // build the resident window tables (PianoPrecomputation::generate, piano.rs:477-504)
 void srs_build_tables(fb_ctx* c) {
     c->u_bases = MsmBases();
-    c->u_bases.n = c->T;
+    c->u_bases.n = c->ncols;
     c->u_bases.pts = c->d_u;
     c->y_bases = MsmBases();
     c->y_bases.n = c->M;
     c->y_bases.pts = c->d_g_tau_y;
     if (c->window_pref < 0) return;
-    if (c->T >= 16) {
-        int cc = c->window_pref > 0 ? c->window_pref : msm_pick_window(c->T, true);
+    if (c->ncols >= 16) {
+        int cc = c->window_pref > 0 ? c->window_pref : msm_pick_window(c->ncols, true);
         int nwin = (256 + cc - 1) / cc;
         G1Affine* tab;
-        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->T * c->nrows * sizeof(G1Affine)));
-        msm_build_table(c->d_u, c->T, c->nrows, cc, nwin, tab, c->pt_a, c->stream);
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->ncols * c->nrows * sizeof(G1Affine)));
+        msm_build_table(c->d_u, c->ncols, c->nrows, cc, nwin, tab, c->pt_a, c->stream);
         c->u_bases.pts = tab;
         c->u_bases.c = cc;
         c->u_bases.nwin = nwin;
@@ -70,12 +70,14 @@ int check_rows(fb_ctx* c, uint64_t& row0, uint64_t& nrows) {
         nrows = c->M;
     }
     if (row0 + nrows > c->M) return ctx_fail(c, FB_ERR_ARG, "row range exceeds 2^machines_scale");
+    uint64_t c0 = c->want_col0, nc = c->want_ncols ? c->want_ncols : c->T;
+    if (c0 + nc > c->T) return ctx_fail(c, FB_ERR_ARG, "column range exceeds 2^(scale - machines_scale)");
     return FB_OK;
 }
 
 MsmBases row_bases(fb_ctx* c, uint64_t i) {
     MsmBases b = c->u_bases;
-    size_t per_row = (size_t)(b.c > 0 ? b.nwin : 1) * c->T;
+    size_t per_row = (size_t)(b.c > 0 ? b.nwin : 1) * c->ncols;
     b.pts = c->u_bases.pts + (i - c->row0) * per_row;
     return b;
 }
@@ -85,6 +87,19 @@ int need_row(fb_ctx* c, uint64_t i, uint64_t cnt) {
     if (i + cnt > c->M) return ctx_fail(c, FB_ERR_ARG, "machine index out of range");
     if (i < c->row0 || i + cnt > c->row0 + c->nrows) return ctx_fail(c, FB_ERR_STATE, "row not resident on this context");
     return FB_OK;
+}
+
+bool col_sharded(fb_ctx* c) { return c->ncols != c->T; }
+int need_full_cols(fb_ctx* c) {
+    if (col_sharded(c)) return ctx_fail(c, FB_ERR_STATE, "column-sharded context: use the *_partial calls and add the parts");
+    return FB_OK;
+}
+
+// MSM of one row over the resident column range: scalars are the FULL row (len)
+void row_msm(fb_ctx* c, uint64_t i, const Fr* d_scalars, size_t len, G1Xyzz* d_out) {
+    size_t lo = c->col0 < len ? c->col0 : len;
+    size_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
+    msm_run(row_bases(c, i), d_scalars + lo, hi - lo, 1, true, d_out, c->msm, c->stream);
 }
 
 // the field half of worker_open on device: d_coeffs (Montgomery, len) ->
@@ -110,6 +125,9 @@ int fb_srs_generate(fb_ctx* c, const uint8_t sx[32], const uint8_t sy[32], uint6
         srs_free(c);
         c->row0 = row0;
         c->nrows = nrows;
+        c->col0 = c->want_col0;
+        c->ncols = c->want_ncols ? c->want_ncols : c->T;
+        const size_t NC = c->ncols;
         cudaStream_t st = c->stream;
         uint8_t* d_sec = c->in_bytes.as<uint8_t>(64);
         FB_CUDA(cudaMemcpyAsync(d_sec, sx, 32, cudaMemcpyHostToDevice, st));
@@ -121,19 +139,24 @@ int fb_srs_generate(fb_ctx* c, const uint8_t sx[32], const uint8_t sy[32], uint6
         Fr* d_r = c->fr_b.as<Fr>(c->M);
         srs_lagrange_at(d_small, (int)c->t, d_l, d_small + 2, st);      // piano.rs:973-988
         srs_lagrange_at(d_small + 1, (int)c->m, d_r, d_small + 5, st);  // :956-971
-        FB_CUDA(cudaMalloc(&c->d_u, nrows * c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_u, nrows * NC * sizeof(G1Affine)));
         FB_CUDA(cudaMalloc(&c->d_g_tau_x, c->T * sizeof(G1Affine)));
         FB_CUDA(cudaMalloc(&c->d_g_tau_y, c->M * sizeof(G1Affine)));
         // U[i][j] = g^(R_i * L_j)  (:995-1007), in slabs of rows to bound the scalar scratch
-        size_t slab = ((size_t)1 << 22) / c->T;
+        size_t slab = ((size_t)1 << 22) / NC;
         if (slab < 1) slab = 1;
         for (uint64_t r = 0; r < nrows; r += slab) {
             size_t rc2 = nrows - r < slab ? nrows - r : slab;
-            Fr* d_prod = c->fr_c.as<Fr>(rc2 * c->T);
-            srs_outer(d_r + row0 + r, rc2, d_l, c->T, d_prod, st);
-            g1_fixed_base_mul(d_prod, rc2 * c->T, c->d_u + r * c->T, c->pt_a, st);
+            Fr* d_prod = c->fr_c.as<Fr>(rc2 * NC);
+            srs_outer(d_r + row0 + r, rc2, d_l + c->col0, NC, d_prod, st);
+            g1_fixed_base_mul(d_prod, rc2 * NC, c->d_u + r * NC, c->pt_a, st);
         }
-        {
+        if (col_sharded(c)) {  // a column shard does not need g^(tau_X^k) (only the setup file does)
+            FB_CUDA(cudaMemsetAsync(c->d_g_tau_x, 0, c->T * sizeof(G1Affine), st));
+            Fr* d_pw = c->fr_c.as<Fr>(c->M);
+            srs_powers(d_small + 1, c->M, d_pw, st);
+            g1_fixed_base_mul(d_pw, c->M, c->d_g_tau_y, c->pt_a, st);
+        } else {
             Fr* d_pw = c->fr_c.as<Fr>(c->T > c->M ? c->T : c->M);
             srs_powers(d_small, c->T, d_pw, st);  // :916-931
             g1_fixed_base_mul(d_pw, c->T, c->d_g_tau_x, c->pt_a, st);
@@ -183,9 +206,11 @@ int fb_srs_load_bytes(fb_ctx* c, const uint8_t* buf, size_t len, int compressed,
         srs_free(c);
         c->row0 = row0;
         c->nrows = nrows;
+        c->col0 = c->want_col0;
+        c->ncols = c->want_ncols ? c->want_ncols : c->T;
         cudaStream_t st = c->stream;
         ctx_reset_err(c);
-        FB_CUDA(cudaMalloc(&c->d_u, nrows * c->T * sizeof(G1Affine)));
+        FB_CUDA(cudaMalloc(&c->d_u, nrows * c->ncols * sizeof(G1Affine)));
         FB_CUDA(cudaMalloc(&c->d_g_tau_x, c->T * sizeof(G1Affine)));
         FB_CUDA(cudaMalloc(&c->d_g_tau_y, c->M * sizeof(G1Affine)));
         auto decode = [&](size_t off, size_t count, G1Affine* dst) {
@@ -203,7 +228,12 @@ int fb_srs_load_bytes(fb_ctx* c, const uint8_t* buf, size_t len, int compressed,
         decode(off_g, 1, d_g);
         decode(off_x, c->T, c->d_g_tau_x);
         decode(off_y, c->M, c->d_g_tau_y);
-        decode(off_u + row0 * c->T * e1, nrows * c->T, c->d_u);
+        if (!col_sharded(c)) {
+            decode(off_u + row0 * c->T * e1, nrows * c->T, c->d_u);
+        } else {
+            for (uint64_t r = 0; r < nrows; r++)
+                decode(off_u + ((row0 + r) * c->T + c->col0) * e1, c->ncols, c->d_u + r * c->ncols);
+        }
         FB_CUDA(cudaMemcpyAsync(&c->g, d_g, sizeof(G1Affine), cudaMemcpyDeviceToHost, st));
         rc = ctx_check_err(c);
         if (rc) {
@@ -241,7 +271,8 @@ int fb_srs_load_file(fb_ctx* c, const char* path, int compressed, uint64_t row0,
 int fb_srs_to_bytes(fb_ctx* c, int compressed, uint8_t* out, size_t cap, size_t* written) {
     return ctx_call(c, [&]() -> int {
         if (!c->srs_ready) return ctx_fail(c, FB_ERR_STATE, "setup not loaded");
-        if (c->row0 != 0 || c->nrows != c->M) return ctx_fail(c, FB_ERR_STATE, "saving needs every row resident");
+        if (c->row0 != 0 || c->nrows != c->M || col_sharded(c))
+            return ctx_fail(c, FB_ERR_STATE, "saving needs every row and column resident");
         const size_t e1 = compressed ? 48 : 96, e2 = compressed ? 96 : 192;
         size_t total = e1 + 8 + c->T * e1 + 8 + c->M * e1 + 16 + c->M * c->T * e1 + 3 * e2;
         if (written) *written = total;
@@ -311,6 +342,7 @@ int fb_commit_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coef
     return ctx_call(c, [&]() -> int {
         int rc = need_row(c, row0, nrows);
         if (rc) return rc;
+        if ((rc = need_full_cols(c))) return rc;
         if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
         if (nrows == 0) return FB_OK;
         ctx_reset_err(c);
@@ -333,6 +365,7 @@ int fb_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs
     return ctx_call(c, [&]() -> int {
         int rc = need_row(c, row0, nrows);
         if (rc) return rc;
+        if ((rc = need_full_cols(c))) return rc;
         if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "Supplied list is longer than the available max width");
         int lg = ilog2_exact(len);
         if (lg < 0) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
@@ -343,10 +376,10 @@ int fb_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs
         uint8_t* d_b = c->in_bytes.as<uint8_t>(nrows * len * 32 + 64);
         FB_CUDA(cudaMemcpyAsync(d_b, coeffs_be, nrows * len * 32, cudaMemcpyHostToDevice, c->stream));
         Fr* d_alpha = ctx_upload_fr(c, c->small, c->pt_a, alpha_be, 1);
-        Fr* d_all = (Fr*)c->msm.misc.get((nrows * len + nrows + 1) * sizeof(Fr));
+        Fr* d_all = (Fr*)c->eng_a.get((nrows * len + nrows + 1) * sizeof(Fr));
         Fr* d_ys = d_all + nrows * len;
         fr_from_be(d_b, d_all, nrows * len, c->d_err, c->stream);
-        G1Xyzz* d_r = (G1Xyzz*)c->msm.order.get((nrows + 1) * sizeof(G1Xyzz));
+        G1Xyzz* d_r = (G1Xyzz*)c->eng_b.get((nrows + 1) * sizeof(G1Xyzz));
         for (uint64_t r = 0; r < nrows; r++) {
             Fr* d_qhat = open_scalars(c, tab, d_all + r * len, len, d_alpha, d_ys + r);
             msm_run(row_bases(c, row0 + r), d_qhat, len, 1, true, d_r + r, c->msm, c->stream);  // piano.rs:228-236
@@ -384,12 +417,12 @@ int fb_master_open(fb_ctx* c, const uint8_t* evals_be, const uint8_t* proofs48, 
         FB_CUDA(cudaMemcpyAsync(d_pb, proofs48, count * 48, cudaMemcpyHostToDevice, st));
         G1Affine* pts = c->pt_a.as<G1Affine>(count + 1);
         g1_decompress_batch(d_pb, pts, count, c->d_err + 1, st);
-        G1Xyzz* d_r = (G1Xyzz*)c->msm.order.get(4 * sizeof(G1Xyzz));
+        G1Xyzz* d_r = (G1Xyzz*)c->eng_b.get(4 * sizeof(G1Xyzz));
         g1_sum_affine(pts, count, d_r, c->scan, st);
         // f(Y, alpha) = iNTT_right(evals); z = f(beta); q1 = (f - z)/(Y - beta)  (:268-282)
         const NttTables& tab = ctx_ntt_tables(c, lg);
         Fr* d_ev = ctx_upload_fr(c, c->in_bytes, c->fr_a, evals_be, count);
-        Fr* d_beta = (Fr*)c->msm.misc.get(4 * sizeof(Fr));
+        Fr* d_beta = (Fr*)c->eng_a.get(4 * sizeof(Fr));
         {
             uint8_t* d_bb = c->small.as<uint8_t>(64);
             FB_CUDA(cudaMemcpyAsync(d_bb, beta_be, 32, cudaMemcpyHostToDevice, st));
@@ -415,32 +448,104 @@ int fb_master_open(fb_ctx* c, const uint8_t* evals_be, const uint8_t* proofs48, 
     });
 }
 
-// ------------------------------------------------------- device-resident calls
+// ------------------------------------------- partial (column-shard) + device calls
+// out_fmt 48: compressed final result (whole-row contexts only); 96: uncompressed
+// partial over the resident column range, to be added across shards (fb_g1_sum).
+static void points_out_fmt(fb_ctx* c, const G1Xyzz* d_xyzz, uint8_t* d_out, int fmt) {
+    if (fmt == 48) {
+        ctx_points_out(c, d_xyzz, 1, d_out);
+        return;
+    }
+    G1Affine* aff = c->pt_b.as<G1Affine>(2);
+    prof_mark("out.affine_compress", c->stream);
+    g1_xyzz_to_affine_batch(d_xyzz, aff, 1, c->stream);
+    g1_serialize_batch(aff, d_out, 1, c->stream);
+}
+
+static int dev_commit(fb_ctx* c, uint64_t i, const Fr* d_coeffs, uint64_t len, uint8_t* d_out, int fmt) {
+    int rc = need_row(c, i, 1);
+    if (rc) return rc;
+    if (fmt == 48 && (rc = need_full_cols(c))) return rc;
+    if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
+    G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
+    row_msm(c, i, d_coeffs, len, d_r);
+    points_out_fmt(c, d_r, d_out, fmt);
+    return FB_OK;
+}
+
+// d_out: 32 bytes y (big-endian) then the point in `fmt`
+static int dev_open(fb_ctx* c, uint64_t i, const Fr* d_coeffs, uint64_t len, const Fr* d_alpha, uint8_t* d_out, int fmt) {
+    int rc = need_row(c, i, 1);
+    if (rc) return rc;
+    if (fmt == 48 && (rc = need_full_cols(c))) return rc;
+    int lg = ilog2_exact(len);
+    if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+    const NttTables& tab = ctx_ntt_tables(c, lg);
+    Fr* d_y = (Fr*)c->eng_a.get(4 * sizeof(Fr));
+    Fr* d_qhat = open_scalars(c, tab, d_coeffs, len, d_alpha, d_y);
+    G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
+    row_msm(c, i, d_qhat, len, d_r);
+    fr_to_be(d_y, d_out, 1, c->stream);
+    points_out_fmt(c, d_r, d_out + 32, fmt);
+    return FB_OK;
+}
+
+int fb_ctx_set_col_shard(fb_ctx* c, uint64_t col0, uint64_t ncols) {
+    if (!c) return FB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (col0 + ncols > c->T) return ctx_fail(c, FB_ERR_ARG, "column range exceeds 2^(scale - machines_scale)");
+    c->want_col0 = ncols ? col0 : 0;
+    c->want_ncols = ncols;
+    return FB_OK;
+}
+
 int fb_dev_worker_commit(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, void* d_out48) {
+    return ctx_call(c, [&]() -> int { return dev_commit(c, i, (const Fr*)d_coeffs, len, (uint8_t*)d_out48, 48); });
+}
+int fb_dev_worker_commit_partial(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, void* d_out96) {
+    return ctx_call(c, [&]() -> int { return dev_commit(c, i, (const Fr*)d_coeffs, len, (uint8_t*)d_out96, 96); });
+}
+int fb_dev_worker_open(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, const void* d_alpha, void* d_out80) {
     return ctx_call(c, [&]() -> int {
-        int rc = need_row(c, i, 1);
-        if (rc) return rc;
-        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
-        G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
-        msm_run(row_bases(c, i), (const Fr*)d_coeffs, len, 1, true, d_r, c->msm, c->stream);
-        ctx_points_out(c, d_r, 1, (uint8_t*)d_out48);
-        return FB_OK;
+        return dev_open(c, i, (const Fr*)d_coeffs, len, (const Fr*)d_alpha, (uint8_t*)d_out80, 48);
+    });
+}
+int fb_dev_worker_open_partial(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, const void* d_alpha,
+                               void* d_out128) {
+    return ctx_call(c, [&]() -> int {
+        return dev_open(c, i, (const Fr*)d_coeffs, len, (const Fr*)d_alpha, (uint8_t*)d_out128, 96);
     });
 }
 
-int fb_dev_worker_open(fb_ctx* c, uint64_t i, const void* d_coeffs, uint64_t len, const void* d_alpha, void* d_out80) {
+int fb_worker_commit_partial(fb_ctx* c, uint64_t i, const uint8_t* coeffs_be, uint64_t len, uint8_t out96[96]) {
     return ctx_call(c, [&]() -> int {
-        int rc = need_row(c, i, 1);
+        ctx_reset_err(c);
+        Fr* d_s = ctx_upload_fr(c, c->in_bytes, c->fr_a, coeffs_be, len);
+        uint8_t* d_ob = c->out_bytes.as<uint8_t>(128);
+        int rc = dev_commit(c, i, d_s, len, d_ob, 96);
         if (rc) return rc;
-        int lg = ilog2_exact(len);
-        if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
-        const NttTables& tab = ctx_ntt_tables(c, lg);
-        Fr* d_y = (Fr*)c->msm.misc.get(4 * sizeof(Fr));
-        Fr* d_qhat = open_scalars(c, tab, (const Fr*)d_coeffs, len, (const Fr*)d_alpha, d_y);
-        G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
-        msm_run(row_bases(c, i), d_qhat, len, 1, true, d_r, c->msm, c->stream);
-        fr_to_be(d_y, (uint8_t*)d_out80, 1, c->stream);
-        ctx_points_out(c, d_r, 1, (uint8_t*)d_out80 + 32);
+        FB_CUDA(cudaMemcpyAsync(out96, d_ob, 96, cudaMemcpyDeviceToHost, c->stream));
+        return ctx_check_err(c);
+    });
+}
+
+int fb_worker_open_partial(fb_ctx* c, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                           uint8_t out_y_be[32], uint8_t out96[96]) {
+    return ctx_call(c, [&]() -> int {
+        ctx_reset_err(c);
+        Fr* d_alpha = ctx_upload_fr(c, c->small, c->pt_a, alpha_be, 1);
+        Fr* d_s = (Fr*)c->eng_b.get((len + 1) * sizeof(Fr));
+        uint8_t* d_b = c->in_bytes.as<uint8_t>(len * 32 + 64);
+        FB_CUDA(cudaMemcpyAsync(d_b, coeffs_be, len * 32, cudaMemcpyHostToDevice, c->stream));
+        fr_from_be(d_b, d_s, len, c->d_err, c->stream);
+        uint8_t* d_ob = c->out_bytes.as<uint8_t>(128);
+        int rc = dev_open(c, i, d_s, len, d_alpha, d_ob, 96);
+        if (rc) return rc;
+        FB_CUDA(cudaMemcpyAsync(c->h_pinned, d_ob, 128, cudaMemcpyDeviceToHost, c->stream));
+        rc = ctx_check_err(c);
+        if (rc) return rc;
+        memcpy(out_y_be, c->h_pinned, 32);
+        memcpy(out96, c->h_pinned + 32, 96);
         return FB_OK;
     });
 }

@@ -140,20 +140,67 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
     return r;
 }
 
-// one thread per bucket: bucket[b] = sum of its (signed) points
-__global__ void __launch_bounds__(128) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
-                                                    const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends,
-                                                    uint32_t nbuckets, G1Xyzz* __restrict__ buckets) {
+// ---- balanced bucket accumulation.  A bucket with cnt entries is cut into
+// nt = max(ceil(cnt/cap), isqrt(cnt)) tasks of equal length (1 task when cnt <= cap),
+// so that no thread walks more than ~cap entries however skewed the digits are (the
+// top window of a 255-bit scalar, or structured inputs such as all-equal scalars,
+// put thousands of points into a few buckets).  One thread per task produces a
+// partial sum; one thread per bucket then adds its partials.
+__device__ __forceinline__ uint32_t tasks_for(uint32_t cnt, uint32_t cap) {
+    if (cnt <= cap) return cnt ? 1u : 0u;
+    uint32_t a = (cnt + cap - 1) / cap;
+    uint32_t r = (uint32_t)sqrtf((float)cnt);
+    return a > r ? a : r;
+}
+
+__global__ void __launch_bounds__(256) k_task_count(const uint32_t* __restrict__ counts, uint32_t nbuckets, uint32_t cap,
+                                                    uint32_t* __restrict__ ntasks) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nbuckets) ntasks[b] = tasks_for(counts[b], cap);
+}
+
+// task t of bucket b covers entries [start, start+len)
+__global__ void __launch_bounds__(256) k_task_fill(const uint32_t* __restrict__ counts, const uint32_t* __restrict__ offsets,
+                                                   const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ toff,
+                                                   uint32_t nbuckets, uint2* __restrict__ tasks, uint32_t* __restrict__ total) {
     uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nbuckets) return;
-    uint32_t lo = offsets[b], hi = ends[b];  // ends = cursor array after the scatter
+    uint32_t nt = ntasks[b], cnt = counts[b], base = offsets[b], t0 = toff[b];
+    if (b == nbuckets - 1) *total = t0 + nt;
+    if (!nt) return;
+    uint32_t len = (cnt + nt - 1) / nt;
+    for (uint32_t k = 0; k < nt; k++) {
+        uint32_t lo = k * len;
+        uint32_t l = lo >= cnt ? 0u : (cnt - lo < len ? cnt - lo : len);
+        tasks[t0 + k] = make_uint2(base + lo, l);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
+                                                    const uint2* __restrict__ tasks, const uint32_t* __restrict__ total,
+                                                    G1Xyzz* __restrict__ partial) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *total) return;
+    uint2 tk = tasks[t];
     G1Xyzz acc = G1Xyzz::inf();
-    for (uint32_t e = lo; e < hi; e++) {
+    for (uint32_t e = tk.x; e < tk.x + tk.y; e++) {
         uint32_t ent = sorted[e];
         G1Affine p = ldg_affine(pts + (ent & 0x7fffffffu));
         if (ent >> 31) p.y = fe_neg<FpParams>(p.y);
         g1_add_mixed(acc, p);
     }
+    partial[t] = acc;
+}
+
+__global__ void __launch_bounds__(128) k_combine(const G1Xyzz* __restrict__ partial, const uint32_t* __restrict__ ntasks,
+                                                 const uint32_t* __restrict__ toff, uint32_t nbuckets,
+                                                 G1Xyzz* __restrict__ buckets) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbuckets) return;
+    uint32_t nt = ntasks[b], t0 = toff[b];
+    G1Xyzz acc = G1Xyzz::inf();
+    if (nt) acc = partial[t0];
+    for (uint32_t k = 1; k < nt; k++) g1_add(acc, partial[t0 + k]);
     buckets[b] = acc;
 }
 
@@ -329,8 +376,24 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     a2.counts = cursor;
     prof_mark("msm.scatter", st);
     (++fb::g_launches, k_digits<true><<<gb, 256, 0, st>>>(a2));
+    prof_mark("msm.tasks", st);
+    const uint64_t entries = (uint64_t)n * nwin;
+    uint32_t cap = (uint32_t)(2 * entries / nbuckets);
+    if (cap < 32) cap = 32;
+    if (cap > 512) cap = 512;
+    const uint32_t max_tasks = nbuckets + (uint32_t)(entries / cap) + 1;
+    uint32_t* ntasks = s.order.as<uint32_t>((size_t)2 * nbuckets + 4);
+    uint32_t* toff = ntasks + nbuckets;
+    uint32_t* d_total = toff + nbuckets;
+    uint2* tasks = s.misc.as<uint2>(max_tasks);
+    G1Xyzz* partial = s.seg_t.as<G1Xyzz>(max_tasks);
+    (++fb::g_launches, k_task_count<<<(nbuckets + 255) / 256, 256, 0, st>>>(counts, nbuckets, cap, ntasks));
+    exclusive_scan(ntasks, toff, nbuckets, s.block_sums, st);
+    (++fb::g_launches, k_task_fill<<<(nbuckets + 255) / 256, 256, 0, st>>>(counts, offsets, ntasks, toff, nbuckets, tasks, d_total));
     prof_mark("msm.accumulate", st);
-    (++fb::g_launches, k_accumulate<<<(nbuckets + 127) / 128, 128, 0, st>>>(bases.pts, sorted, offsets, cursor, nbuckets, buckets));
+    (++fb::g_launches, k_accumulate<<<(max_tasks + 127) / 128, 128, 0, st>>>(bases.pts, sorted, tasks, d_total, partial));
+    prof_mark("msm.combine", st);
+    (++fb::g_launches, k_combine<<<(nbuckets + 127) / 128, 128, 0, st>>>(partial, ntasks, toff, nbuckets, buckets));
 
     // bucket reduction
     prof_mark("msm.reduce", st);

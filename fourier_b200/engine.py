@@ -210,6 +210,33 @@ class PianoBackend:
         return ([ys.raw[k * 32:(k + 1) * 32] for k in range(nrows)],
                 [pis.raw[k * 48:(k + 1) * 48] for k in range(nrows)])
 
+    # -- column shards (one MSM over several GPUs) ----------------------------------
+    def set_col_shard(self, col0: int, ncols: int):
+        """Keep only columns [col0, col0+ncols) resident (applies at the next setup/load)."""
+        self._chk(self._lib.fb_ctx_set_col_shard(self._ctx, col0, ncols))
+
+    def worker_commit_partial(self, i: int, coeffs: ScalarVec) -> bytes:
+        buf, n = pack_scalars(coeffs)
+        out = C.create_string_buffer(96)
+        self._chk(self._lib.fb_worker_commit_partial(self._ctx, i, _lib.addr(buf), n, C.addressof(out)))
+        return out.raw
+
+    def worker_open_partial(self, i: int, coeffs: ScalarVec, alpha) -> Tuple[bytes, bytes]:
+        buf, n = pack_scalars(coeffs)
+        a = pack_scalar(alpha)
+        y = C.create_string_buffer(FR_BYTES)
+        pi = C.create_string_buffer(96)
+        self._chk(self._lib.fb_worker_open_partial(self._ctx, i, _lib.addr(buf), n, _lib.addr(a), C.addressof(y),
+                                                   C.addressof(pi)))
+        return y.raw, pi.raw
+
+    def dev_worker_commit_partial(self, i: int, d_coeffs, count: int, d_out96):
+        self._chk(self._lib.fb_dev_worker_commit_partial(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_out96)))
+
+    def dev_worker_open_partial(self, i: int, d_coeffs, count: int, d_alpha, d_out128):
+        self._chk(self._lib.fb_dev_worker_open_partial(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_alpha),
+                                                       _lib.addr(d_out128)))
+
     # -- master side ---------------------------------------------------------------
     def master_commit(self, commitments) -> bytes:
         """piano.rs:164-175."""

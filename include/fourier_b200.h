@@ -57,6 +57,13 @@ int fb_ctx_sync(fb_ctx* ctx);
  * (0 = pick from the row length; -1 = no tables: plain Pippenger per call) */
 int fb_ctx_set_window(fb_ctx* ctx, int window_bits);
 
+/* Column sharding (one MSM split over GPUs by point ranges): keep only columns
+ * [col0, col0+ncols) of every resident row.  Takes effect at the next SRS
+ * generate / load; ncols = 0 restores whole rows.  A column-sharded context
+ * serves the *_partial calls below; the 96-byte partial sums of all shards are
+ * added with fb_g1_sum (format 96). */
+int fb_ctx_set_col_shard(fb_ctx* ctx, uint64_t col0, uint64_t ncols);
+
 /* ---- SRS -------------------------------------------------------------------
  * Rows [row0, row0+nrows) of U are kept resident on this context's device
  * (nrows = 0 means all 2^m rows).  Sharding rows over GPUs = one context per GPU
@@ -90,6 +97,12 @@ int fb_commit_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* co
                    uint8_t* out48s);
 int fb_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len,
                  const uint8_t alpha_be[32], uint8_t* out_ys_be, uint8_t* out_proof48s);
+
+/* partial results over the resident column range (uncompressed, 96 bytes); the
+ * coefficient vector is always the FULL row */
+int fb_worker_commit_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, uint8_t out96[96]);
+int fb_worker_open_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                           uint8_t out_y_be[32], uint8_t out96[96]);
 
 /* ---- engine: master side ------------------------------------------------------
  * replaces PianoBackend::master_commit (piano.rs:164-175): sum of the commitments */
@@ -137,6 +150,11 @@ int fb_dev_worker_commit(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint6
 /* d_out: 32 bytes y (big-endian) followed by 48 bytes proof */
 int fb_dev_worker_open(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
                        void* d_out80);
+
+int fb_dev_worker_commit_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, void* d_out96);
+/* d_out: 32 bytes y followed by 96 bytes partial proof */
+int fb_dev_worker_open_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
+                               void* d_out128);
 
 /* number of kernel launches issued by this library so far */
 uint64_t fb_launch_count(const fb_ctx* ctx);

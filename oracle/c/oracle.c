@@ -102,46 +102,130 @@ static inline void mod_sub(u64* r, const u64* a, const u64* b, const u64* m, int
     if (br) add_n(t, t, m, n);
     for (int i = 0; i < n; i++) r[i] = t[i];
 }
-/* Montgomery product, coarsely integrated operand scanning */
-static inline void mont_mul(u64* r, const u64* a, const u64* b, const u64* m, u64 inv, int n) {
-    u64 t[FPN + 2];
-    for (int i = 0; i < n + 2; i++) t[i] = 0;
-    for (int i = 0; i < n; i++) {
-        u128 c = 0;
-        for (int j = 0; j < n; j++) {
-            c += (u128)a[j] * b[i] + t[j];
-            t[j] = (u64)c;
-            c >>= 64;
-        }
-        c += t[n];
-        t[n] = (u64)c;
-        t[n + 1] = (u64)(c >> 64);
-        u64 q = t[0] * inv;
-        c = (u128)q * m[0] + t[0];
-        c >>= 64;
-        for (int j = 1; j < n; j++) {
-            c += (u128)q * m[j] + t[j];
-            t[j - 1] = (u64)c;
-            c >>= 64;
-        }
-        c += t[n];
-        t[n - 1] = (u64)c;
-        t[n] = t[n + 1] + (u64)(c >> 64);
+/* Montgomery product, coarsely integrated operand scanning; one fully unrolled
+ * instance per limb count (the generic-n form was 5x slower) */
+#define DEFINE_MONT_MUL(NAME, N)                                                              \
+    static inline __attribute__((always_inline)) void NAME(u64* r, const u64* a, const u64* b, \
+                                                           const u64* m, u64 inv) {            \
+        u64 t[N + 2];                                                                         \
+        _Pragma("GCC unroll 8") for (int i = 0; i < N + 2; i++) t[i] = 0;                     \
+        _Pragma("GCC unroll 8") for (int i = 0; i < N; i++) {                                 \
+            u128 c = 0;                                                                       \
+            _Pragma("GCC unroll 8") for (int j = 0; j < N; j++) {                             \
+                c += (u128)a[j] * b[i] + t[j];                                                \
+                t[j] = (u64)c;                                                                \
+                c >>= 64;                                                                     \
+            }                                                                                 \
+            c += t[N];                                                                        \
+            t[N] = (u64)c;                                                                    \
+            t[N + 1] = (u64)(c >> 64);                                                        \
+            u64 q = t[0] * inv;                                                               \
+            c = (u128)q * m[0] + t[0];                                                        \
+            c >>= 64;                                                                         \
+            _Pragma("GCC unroll 8") for (int j = 1; j < N; j++) {                             \
+                c += (u128)q * m[j] + t[j];                                                   \
+                t[j - 1] = (u64)c;                                                            \
+                c >>= 64;                                                                     \
+            }                                                                                 \
+            c += t[N];                                                                        \
+            t[N - 1] = (u64)c;                                                                \
+            t[N] = t[N + 1] + (u64)(c >> 64);                                                 \
+        }                                                                                     \
+        u64 s[N];                                                                             \
+        u64 br = 0;                                                                           \
+        _Pragma("GCC unroll 8") for (int i = 0; i < N; i++) {                                 \
+            u128 d = (u128)t[i] - m[i] - br;                                                  \
+            s[i] = (u64)d;                                                                    \
+            br = (u64)(d >> 64) & 1;                                                          \
+        }                                                                                     \
+        u64 keep = (t[N] == 0 && br) ? ~(u64)0 : 0;                                           \
+        _Pragma("GCC unroll 8") for (int i = 0; i < N; i++) r[i] = (t[i] & keep) | (s[i] & ~keep); \
     }
-    u64 s[FPN];
-    u64 br = sub_n(s, t, m, n);
-    const u64* src = (t[n] || !br) ? s : t;
-    for (int i = 0; i < n; i++) r[i] = src[i];
+DEFINE_MONT_MUL(mont_mul4, 4)
+DEFINE_MONT_MUL(mont_mul6, 6)
+#if defined(__x86_64__) && defined(__BMI2__) && defined(__ADX__)
+/* t[0..5] += x[0..3] * y with the two carry chains of mulx/adcx/adox */
+static inline __attribute__((always_inline)) void mac_row4(u64* t, const u64* x, u64 y) {
+    u64 lo, hi, z;
+    __asm__(
+        "xorq %[z], %[z]\n\t"
+        "mulxq 0(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t0]\n\t adoxq %[hi], %[t1]\n\t"
+        "mulxq 8(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t1]\n\t adoxq %[hi], %[t2]\n\t"
+        "mulxq 16(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t2]\n\t adoxq %[hi], %[t3]\n\t"
+        "mulxq 24(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t3]\n\t adoxq %[hi], %[t4]\n\t"
+        "adcxq %[z], %[t4]\n\t adoxq %[z], %[t5]\n\t adcxq %[z], %[t5]\n\t"
+        : [t0] "+r"(t[0]), [t1] "+r"(t[1]), [t2] "+r"(t[2]), [t3] "+r"(t[3]), [t4] "+r"(t[4]), [t5] "+r"(t[5]), [lo] "=&r"(lo), [hi] "=&r"(hi), [z] "=&r"(z)
+        : [x] "r"(x), "d"(y), "m"(*(const u64(*)[4])x)
+        : "cc");
 }
+static inline __attribute__((always_inline)) void mont_mul4x(u64* r, const u64* a, const u64* b, const u64* m, u64 inv) {
+    u64 t[6] = {0};
+    for (int i = 0; i < 4; i++) {
+        mac_row4(t, a, b[i]);
+        mac_row4(t, m, t[0] * inv);
+        for (int k = 0; k < 5; k++) t[k] = t[k + 1];
+        t[5] = 0;
+    }
+    u64 s[4];
+    u64 br = 0;
+    for (int i = 0; i < 4; i++) {
+        u128 d = (u128)t[i] - m[i] - br;
+        s[i] = (u64)d;
+        br = (u64)(d >> 64) & 1;
+    }
+    u64 keep = (t[4] == 0 && br) ? ~(u64)0 : 0;
+    for (int i = 0; i < 4; i++) r[i] = (t[i] & keep) | (s[i] & ~keep);
+}
+#else
+#define mont_mul4x mont_mul4
+#endif
+#if defined(__x86_64__) && defined(__BMI2__) && defined(__ADX__)
+/* t[0..7] += x[0..5] * y with the two carry chains of mulx/adcx/adox */
+static inline __attribute__((always_inline)) void mac_row6(u64* t, const u64* x, u64 y) {
+    u64 lo, hi, z;
+    __asm__(
+        "xorq %[z], %[z]\n\t"
+        "mulxq 0(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t0]\n\t adoxq %[hi], %[t1]\n\t"
+        "mulxq 8(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t1]\n\t adoxq %[hi], %[t2]\n\t"
+        "mulxq 16(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t2]\n\t adoxq %[hi], %[t3]\n\t"
+        "mulxq 24(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t3]\n\t adoxq %[hi], %[t4]\n\t"
+        "mulxq 32(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t4]\n\t adoxq %[hi], %[t5]\n\t"
+        "mulxq 40(%[x]), %[lo], %[hi]\n\t adcxq %[lo], %[t5]\n\t adoxq %[hi], %[t6]\n\t"
+        "adcxq %[z], %[t6]\n\t adoxq %[z], %[t7]\n\t adcxq %[z], %[t7]\n\t"
+        : [t0] "+r"(t[0]), [t1] "+r"(t[1]), [t2] "+r"(t[2]), [t3] "+r"(t[3]), [t4] "+r"(t[4]), [t5] "+r"(t[5]), [t6] "+r"(t[6]), [t7] "+r"(t[7]), [lo] "=&r"(lo), [hi] "=&r"(hi), [z] "=&r"(z)
+        : [x] "r"(x), "d"(y), "m"(*(const u64(*)[6])x)
+        : "cc");
+}
+static inline __attribute__((always_inline)) void mont_mul6x(u64* r, const u64* a, const u64* b, const u64* m, u64 inv) {
+    u64 t[8] = {0};
+    for (int i = 0; i < 6; i++) {
+        mac_row6(t, a, b[i]);
+        mac_row6(t, m, t[0] * inv);
+        for (int k = 0; k < 7; k++) t[k] = t[k + 1];
+        t[7] = 0;
+    }
+    u64 s[6];
+    u64 br = 0;
+    for (int i = 0; i < 6; i++) {
+        u128 d = (u128)t[i] - m[i] - br;
+        s[i] = (u64)d;
+        br = (u64)(d >> 64) & 1;
+    }
+    u64 keep = (t[6] == 0 && br) ? ~(u64)0 : 0;
+    for (int i = 0; i < 6; i++) r[i] = (t[i] & keep) | (s[i] & ~keep);
+}
+#else
+#define mont_mul6x mont_mul6
+#endif
 
 typedef struct { u64 v[FRN]; } fr_t;
 typedef struct { u64 v[FPN]; } fp_t;
 
-static inline void fr_mul(fr_t* r, const fr_t* a, const fr_t* b) { mont_mul(r->v, a->v, b->v, FR_MOD, FR_INV, FRN); }
+static inline void fr_mul(fr_t* r, const fr_t* a, const fr_t* b) { mont_mul4x(r->v, a->v, b->v, FR_MOD, FR_INV); }
 static inline void fr_add(fr_t* r, const fr_t* a, const fr_t* b) { mod_add(r->v, a->v, b->v, FR_MOD, FRN); }
 static inline void fr_sub(fr_t* r, const fr_t* a, const fr_t* b) { mod_sub(r->v, a->v, b->v, FR_MOD, FRN); }
-static inline void fp_mul(fp_t* r, const fp_t* a, const fp_t* b) { mont_mul(r->v, a->v, b->v, FP_MOD, FP_INV, FPN); }
-static inline void fp_sqr(fp_t* r, const fp_t* a) { mont_mul(r->v, a->v, a->v, FP_MOD, FP_INV, FPN); }
+static inline void fp_mul(fp_t* r, const fp_t* a, const fp_t* b) { mont_mul6x(r->v, a->v, b->v, FP_MOD, FP_INV); }
+static inline void fp_sqr(fp_t* r, const fp_t* a) { mont_mul6x(r->v, a->v, a->v, FP_MOD, FP_INV); }
 static inline void fp_add(fp_t* r, const fp_t* a, const fp_t* b) { mod_add(r->v, a->v, b->v, FP_MOD, FPN); }
 static inline void fp_sub(fp_t* r, const fp_t* a, const fp_t* b) { mod_sub(r->v, a->v, b->v, FP_MOD, FPN); }
 static inline int fp_is_zero(const fp_t* a) { return is_zero_n(a->v, FPN); }

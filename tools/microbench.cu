@@ -193,9 +193,19 @@ int main() {
         CK(cudaMemcpy(&bad, dbad, 4, cudaMemcpyDeviceToHost));
         printf("{\"check\": \"fp_mul chain vs portable + identities\", \"n\": %d, \"mismatches\": %d}\n", N, bad);
         CK(cudaMemset(dbad, 0, 4));
-        k_check<FrParams><<<N / 256, 256>>>((Fr*)da, (Fr*)db, N, dbad);  // reinterpret: values < 2^252
+        {
+            Fr *hra = (Fr*)malloc(sizeof(Fr) * N), *hrb = (Fr*)malloc(sizeof(Fr) * N);
+            fill_random<FrParams>(hra, N, 3);
+            fill_random<FrParams>(hrb, N, 4);
+            CK(cudaMemcpy(da, hra, sizeof(Fr) * N, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(db, hrb, sizeof(Fr) * N, cudaMemcpyHostToDevice));
+            free(hra);
+            free(hrb);
+        }
+        k_check<FrParams><<<N / 256, 256>>>((Fr*)da, (Fr*)db, N, dbad);
         CK(cudaMemcpy(&bad, dbad, 4, cudaMemcpyDeviceToHost));
         printf("{\"check\": \"fr_mul chain vs portable + identities\", \"n\": %d, \"mismatches\": %d}\n", N, bad);
+        CK(cudaMemcpy(da, ha, sizeof(Fp) * N, cudaMemcpyHostToDevice));
         const int iters = 256;
         int nthreads = sms * 2048;  // full occupancy worth of threads
         if (nthreads > N) nthreads = N;
