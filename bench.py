@@ -39,6 +39,7 @@ SCALE = int(os.environ.get("FB_BENCH_SCALE", "20"))
 SECRET_X, SECRET_Y = bytes([1] * 32), bytes([2] * 32)
 SEED_COEFFS, SEED_ALPHA = 31, 33
 METRIC = "kzg_commit_open_ms_deg2^%d" % SCALE
+WINDOW = int(os.environ.get("FB_BENCH_WINDOW", "0"))  # 0: the library's own choice
 # algorithmic work per unit
 MSM_BYTES_PER_POINT = 128          # 32-byte scalar + 96-byte affine point
 MSM_MAD_PER_POINT = {12: 66000, 20: 48000, 24: 39000}
@@ -161,7 +162,7 @@ def own_arm(args):
     T = n
 
     # ---- setup (untimed): SRS resident in HBM with its window tables
-    be = PianoBackend(SCALE, 0, device=local)
+    be = PianoBackend(SCALE, 0, device=local, window_bits=WINDOW)
     # a non-default torch stream: the library launches on it and torch.cuda.Event times it
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
@@ -270,6 +271,9 @@ def own_arm(args):
     if rank == 0:
         peaks = load_peaks()
         int_peak, int_src = load_int_peak()
+        lg = max(ncols.bit_length() - 1, 1)
+        wbits = WINDOW if WINDOW else max(4, min(20, lg - 1))   # msm_pick_window(tabulated)
+        table_windows = (255 + wbits - 1) // wbits
         acc_ms, acc_cnt = prof.get("msm.accumulate", (0.0, 1))
         acc_avg_s = acc_ms / max(acc_cnt, 1) * 1e-3
         pts_per_launch = ncols
@@ -288,7 +292,7 @@ def own_arm(args):
                                    "bit-exact vs CPU oracle" % (SCALE, SCALE),
                        "parallelism": "1 GPU" if world == 1 else "MSM point ranges over %d GPUs + all-gather of 224-byte partials" % world,
                        "l2": "inputs larger than L2: window tables %.2f GB per GPU + 32 MiB coefficients" %
-                             (13 * ncols * 96 / 1e9), "srs_setup_s": round(setup_s, 2), "seed": [SEED_COEFFS, SEED_ALPHA]},
+                             (table_windows * ncols * 96 / 1e9), "window_bits": wbits, "srs_setup_s": round(setup_s, 2), "seed": [SEED_COEFFS, SEED_ALPHA]},
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * n * 32 + 32, "d2h_bytes_per_step": 48 + 32 + 48
                     if world == 1 else 96 + 32 + 96 + world * 224},
             "gpu_launches": int(launches),

@@ -284,7 +284,7 @@ int fb_bases_precompute(fb_ctx* c, fb_bases* b, int window_bits) {
         if (!b) return ctx_fail(c, FB_ERR_ARG, "null base set");
         int cc = window_bits > 0 ? window_bits : msm_pick_window(b->b.n, true);
         if (cc < 4 || cc > 24) return ctx_fail(c, FB_ERR_ARG, "window bits out of range");
-        int nwin = (256 + cc - 1) / cc;
+        int nwin = msm_num_windows(cc);
         G1Affine* tab;
         FB_CUDA(cudaMalloc(&tab, (size_t)nwin * b->b.n * sizeof(G1Affine)));
         msm_build_table(b->raw, b->b.n, 1, cc, nwin, tab, c->pt_a, c->stream);

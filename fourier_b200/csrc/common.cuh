@@ -137,6 +137,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
 void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, G1Affine* d_out, DevBuf& scratch,
                      cudaStream_t st);
 int msm_pick_window(size_t n, bool tabulated);
+int msm_num_windows(int c);  // ceil(255 / c)
 
 // -------------------------------------------------------------- points (g1ops.cu)
 void g1_decompress_batch(const uint8_t* d_in48, G1Affine* d_out, size_t n, int* d_err, cudaStream_t st);

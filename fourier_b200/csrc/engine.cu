@@ -43,7 +43,8 @@ void srs_build_tables(fb_ctx* c) {
     if (c->window_pref < 0) return;
     if (c->ncols >= 16) {
         int cc = c->window_pref > 0 ? c->window_pref : msm_pick_window(c->ncols, true);
-        int nwin = (256 + cc - 1) / cc;
+        if (cc < 2 || cc > 24) throw CudaError{"window bits out of range (2..24)"};
+        int nwin = msm_num_windows(cc);
         G1Affine* tab;
         FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->ncols * c->nrows * sizeof(G1Affine)));
         msm_build_table(c->d_u, c->ncols, c->nrows, cc, nwin, tab, c->pt_a, c->stream);
@@ -53,7 +54,7 @@ void srs_build_tables(fb_ctx* c) {
     }
     if (c->M >= 16) {
         int cc = msm_pick_window(c->M, true);
-        int nwin = (256 + cc - 1) / cc;
+        int nwin = msm_num_windows(cc);
         G1Affine* tab;
         FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->M * sizeof(G1Affine)));
         msm_build_table(c->d_g_tau_y, c->M, 1, cc, nwin, tab, c->pt_a, c->stream);

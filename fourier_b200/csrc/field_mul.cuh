@@ -189,6 +189,98 @@ FB_HD Fe<P> fe_inv(const Fe<P>& a) {  // a^(m-2); inv(0) = 0
     return fe_pow<P, P::N>(a, e);
 }
 
+// Low-latency inversion for ONE element on ONE thread (the XYZZ -> affine step of a
+// single MSM result): Kaliski's almost-Montgomery inverse, a binary extended GCD of
+// <= 2*bits shift/subtract rounds on the limbs, instead of the ~1.5*bits dependent
+// Montgomery multiplies of Fermat's a^(m-2).  Input and output in Montgomery form;
+// inv(0) = 0.  Data-dependent branches: use fe_inv (branch-free) in warp-wide code.
+template <class P>
+FB_HD Fe<P> fe_inv_gcd(const Fe<P>& a) {
+    constexpr int N = P::N;
+    if (a.is_zero()) return a;
+    uint32_t u[N], v[N], r[N], s[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        u[i] = P::mod(i);
+        v[i] = a.v[i];
+        r[i] = 0;
+        s[i] = 0;
+    }
+    s[0] = 1;
+    int k = 0;
+    auto shr1 = [](uint32_t* x) {
+#pragma unroll
+        for (int i = 0; i < N - 1; i++) x[i] = (x[i] >> 1) | (x[i + 1] << 31);
+        x[N - 1] >>= 1;
+    };
+    auto shl1 = [](uint32_t* x) {
+#pragma unroll
+        for (int i = N - 1; i > 0; i--) x[i] = (x[i] << 1) | (x[i - 1] >> 31);
+        x[0] <<= 1;
+    };
+    auto sub = [](uint32_t* x, const uint32_t* y) {  // x -= y
+        x[0] = sub_cc(x[0], y[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) x[i] = subc_cc(x[i], y[i]);
+        x[N - 1] = subc(x[N - 1], y[N - 1]);
+    };
+    auto add = [](uint32_t* x, const uint32_t* y) {  // x += y
+        x[0] = add_cc(x[0], y[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) x[i] = addc_cc(x[i], y[i]);
+        x[N - 1] = addc(x[N - 1], y[N - 1]);
+    };
+    for (;;) {
+        uint32_t vz = 0;
+#pragma unroll
+        for (int i = 0; i < N; i++) vz |= v[i];
+        if (!vz) break;
+        if (!(u[0] & 1)) {
+            shr1(u);
+            shl1(s);
+        } else if (!(v[0] & 1)) {
+            shr1(v);
+            shl1(r);
+        } else if (!fe_geq<P>(v, u)) {  // u > v
+            sub(u, v);
+            shr1(u);
+            add(r, s);
+            shl1(s);
+        } else {
+            sub(v, u);
+            shr1(v);
+            add(s, r);
+            shl1(r);
+        }
+        k++;
+    }
+    // r < 2m;  m - r = a^-1 * 2^k (mod m),  bits <= k <= 2*bits
+    Fe<P> x;
+    {
+        uint32_t t[N];
+        fe_final_sub<P>(t, r, 0);
+        x.v[0] = sub_cc(P::mod(0), t[0]);
+#pragma unroll
+        for (int i = 1; i < N - 1; i++) x.v[i] = subc_cc(P::mod(i), t[i]);
+        x.v[N - 1] = subc(P::mod(N - 1), t[N - 1]);
+        uint32_t tmp[N];
+        fe_final_sub<P>(tmp, x.v, 0);  // r == 0 cannot happen for a != 0, but keep x < m
+#pragma unroll
+        for (int i = 0; i < N; i++) x.v[i] = tmp[i];
+    }
+    // input was A = a*R: x = A^-1 * 2^k.  Want A^-1 * R^2 = mont(mont(x, R^2), 2^(2*32N - k))
+    x = fe_mul<P>(x, Fe<P>::rsquared());
+    int e = 64 * N - k;  // >= 64N - 2*bits > 0
+    int safe = 32 * N - 4;  // 2^safe < m for both fields (m > 2^(32N-3))
+    int rem = e > safe ? e - safe : 0;
+    e -= rem;
+    Fe<P> b = Fe<P>::zero();
+    b.v[e >> 5] = 1u << (e & 31);
+    x = fe_mul<P>(x, b);
+    for (int i = 0; i < rem; i++) x = fe_dbl<P>(x);
+    return x;
+}
+
 using Fr = Fe<FrParams>;
 using Fp = Fe<FpParams>;
 

@@ -65,7 +65,14 @@ __global__ void __launch_bounds__(128) k_serialize(const G1Affine* __restrict__ 
 __global__ void __launch_bounds__(128) k_to_affine(const G1Xyzz* __restrict__ in, G1Affine* __restrict__ out, size_t n) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = g1_to_affine(in[i]);
+    // few results, one inversion each: the latency of the dependent chain is what
+    // counts here, so the binary-GCD inversion (fe_inv_gcd) replaces Fermat's ladder
+    const G1Xyzz p = in[i];
+    if (p.is_inf()) {
+        out[i] = G1Affine::inf();
+        return;
+    }
+    out[i] = g1_to_affine_with_inv(p, fe_inv_gcd<FpParams>(p.zzz));
 }
 
 // generator comb: tab[w*255 + d-1] = d * 2^(8w) * G  (w < 32, 1 <= d <= 255)

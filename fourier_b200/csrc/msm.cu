@@ -12,18 +12,17 @@
 //   2. exclusive scan of the histogram                       (bucket offsets)
 //   3. k_digits<true>: same digits again; scatter (point index | sign) into its
 //      bucket's slice (a counting sort; order inside a bucket is irrelevant)
-//   4. k_accumulate: one thread per bucket, XYZZ += affine (8M+2S), points gathered
-//      by index from the resident table
-//   5. k_seg_reduce levels: sum_d d*B_d by blocked running sums (segments of 8)
-//   6. k_finish: add the per-window results (doubling ladder when not tabulated)
+//   4. k_accumulate: the sorted entries cut into equal chunks, one per resident thread,
+//      XYZZ += affine (8M+2S), points gathered by index from the resident table;
+//      k_combine adds the partial sums of the buckets that straddle chunks
+//   5. k_fold / k_bits / k_bit_combine: sum_i (i+1)*B_i as row + column sums of the
+//      bucket matrix and bit-sliced weighted sums (plain sums only, short chains)
+//   6. k_window_combine: per-window results (doubling ladder) when not tabulated
 #include "common.cuh"
 
 namespace fb {
 
 namespace {
-
-constexpr int kSegLog = 3;  // bucket-reduction segment = 8 buckets per thread per level
-constexpr int kSeg = 1 << kSegLog;
 
 struct DigitArgs {
     const Fr* scalars;
@@ -33,7 +32,7 @@ struct DigitArgs {
     int c, nwin;
     int mont;       // scalars are in Montgomery form
     int tabulated;  // single bucket set; entry = w*n + j
-    uint32_t buckets_per_win;  // 2^(c-1) + 1 (index = |digit|, index 0 unused)
+    uint32_t buckets_per_win;  // 2^(c-1) (index = |digit| - 1)
     uint32_t* counts;   // histogram (pass 0) / cursors (pass 1)
     uint32_t* sorted;
 };
@@ -45,6 +44,20 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
     const uint32_t row = j / a.len, col = j - row * a.len;
     Fr k = a.scalars[j];
     if (a.mont) k = fe_from_mont<FrParams>(k);
+    // k > (r-1)/2: use -(r - k).  The recoded scalar is < 2^254, so ceil(255/c) windows
+    // hold every signed digit and the top window never carries out (without this a
+    // window count that divides 255 exactly would put ~40% of the scalars' carries
+    // into bucket 1 of an extra window).
+    uint32_t sneg = 0;
+    {
+        Fr hr;
+#pragma unroll
+        for (int i = 0; i < 8; i++) hr.v[i] = (FrParams::mod(i) >> 1) | (i < 7 ? FrParams::mod(i + 1) << 31 : 0u);
+        if (!fe_geq<FrParams>(hr.v, k.v)) {
+            k = fe_neg<FrParams>(k);
+            sneg = 1;
+        }
+    }
     uint32_t kk[9];
 #pragma unroll
     for (int i = 0; i < 8; i++) kk[i] = k.v[i];
@@ -64,13 +77,13 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
         carry = neg;
         uint32_t mag = neg ? (1u << a.c) - raw : raw;
         if (mag == 0) continue;
-        uint32_t bucket = (a.tabulated ? row : row * a.nwin + (uint32_t)w) * a.buckets_per_win + mag;
+        uint32_t bucket = (a.tabulated ? row : row * a.nwin + (uint32_t)w) * a.buckets_per_win + mag - 1;
         if (!SCATTER) {
             atomicAdd(a.counts + bucket, 1u);
         } else {
             uint32_t slot = atomicAdd(a.counts + bucket, 1u);
             uint32_t idx = a.tabulated ? (row * a.nwin + (uint32_t)w) * a.stride + col : row * a.stride + col;
-            a.sorted[slot] = idx | (neg << 31);
+            a.sorted[slot] = idx | ((neg ^ sneg) << 31);
         }
     }
 }
@@ -140,114 +153,225 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
     return r;
 }
 
-// ---- balanced bucket accumulation.  A bucket with cnt entries is cut into
-// nt = max(ceil(cnt/cap), isqrt(cnt)) tasks of equal length (1 task when cnt <= cap),
-// so that no thread walks more than ~cap entries however skewed the digits are (the
-// top window of a 255-bit scalar, or structured inputs such as all-equal scalars,
-// put thousands of points into a few buckets).  One thread per task produces a
-// partial sum; one thread per bucket then adds its partials.
-__device__ __forceinline__ uint32_t tasks_for(uint32_t cnt, uint32_t cap) {
-    if (cnt <= cap) return cnt ? 1u : 0u;
-    uint32_t a = (cnt + cap - 1) / cap;
-    uint32_t r = (uint32_t)sqrtf((float)cnt);
-    return a > r ? a : r;
-}
+// ---- balanced bucket accumulation.  The sorted entry list (E entries, grouped by
+// bucket) is cut into NT equal chunks of K = ceil(E / NT) entries, NT = one wave of
+// resident threads (a multiple of the SM count), whatever the bucket boundaries are:
+// every thread does exactly K mixed additions, so there is no tail and no lane
+// idles while its neighbours walk a longer bucket (the top window of a 255-bit
+// scalar, or structured inputs such as all-equal scalars, put thousands of points
+// into a few buckets).  When the bucket changes inside a chunk the running sum is
+// flushed to partial[bucket + chunk] - (bucket, chunk) pairs are visited in
+// lexicographic order, so that slot is unique - and k_combine adds the partials
+// of each bucket (typically one or two).
+constexpr uint32_t kMinChunk = 8;
 
-__global__ void __launch_bounds__(256) k_task_count(const uint32_t* __restrict__ counts, uint32_t nbuckets, uint32_t cap,
-                                                    uint32_t* __restrict__ ntasks) {
-    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b < nbuckets) ntasks[b] = tasks_for(counts[b], cap);
-}
-
-// task t of bucket b covers entries [start, start+len)
-__global__ void __launch_bounds__(256) k_task_fill(const uint32_t* __restrict__ counts, const uint32_t* __restrict__ offsets,
-                                                   const uint32_t* __restrict__ ntasks, const uint32_t* __restrict__ toff,
-                                                   uint32_t nbuckets, uint2* __restrict__ tasks, uint32_t* __restrict__ total) {
-    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= nbuckets) return;
-    uint32_t nt = ntasks[b], cnt = counts[b], base = offsets[b], t0 = toff[b];
-    if (b == nbuckets - 1) *total = t0 + nt;
-    if (!nt) return;
-    uint32_t len = (cnt + nt - 1) / nt;
-    for (uint32_t k = 0; k < nt; k++) {
-        uint32_t lo = k * len;
-        uint32_t l = lo >= cnt ? 0u : (cnt - lo < len ? cnt - lo : len);
-        tasks[t0 + k] = make_uint2(base + lo, l);
-    }
+__device__ __forceinline__ uint32_t chunk_len(uint32_t E, uint32_t nt) {
+    uint32_t k = (E + nt - 1) / nt;
+    return k < kMinChunk ? kMinChunk : k;
 }
 
 __global__ void __launch_bounds__(128) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
-                                                    const uint2* __restrict__ tasks, const uint32_t* __restrict__ total,
+                                                    const uint32_t* __restrict__ offsets, uint32_t nbuckets,
                                                     G1Xyzz* __restrict__ partial) {
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= *total) return;
-    uint2 tk = tasks[t];
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t E = offsets[nbuckets];
+    const uint32_t K = chunk_len(E, gridDim.x * blockDim.x);
+    uint64_t e0 = (uint64_t)t * K;
+    if (e0 >= E) return;
+    uint32_t e = (uint32_t)e0;
+    const uint32_t end = E - e < K ? E : e + K;
+    // bucket of the first entry: largest b with offsets[b] <= e
+    uint32_t lo = 0, hi = nbuckets;  // invariant: offsets[lo] <= e < offsets[hi]
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (offsets[mid] <= e) lo = mid;
+        else hi = mid;
+    }
+    uint32_t cb = lo;
+    uint32_t next = offsets[cb + 1];
     G1Xyzz acc = G1Xyzz::inf();
-    for (uint32_t e = tk.x; e < tk.x + tk.y; e++) {
+    for (; e < end; e++) {
+        if (e == next) {
+            partial[cb + t] = acc;
+            acc = G1Xyzz::inf();
+            do {
+                cb++;
+                next = offsets[cb + 1];
+            } while (next <= e);
+        }
         uint32_t ent = sorted[e];
         G1Affine p = ldg_affine(pts + (ent & 0x7fffffffu));
         if (ent >> 31) p.y = fe_neg<FpParams>(p.y);
         g1_add_mixed(acc, p);
     }
-    partial[t] = acc;
+    partial[cb + t] = acc;
 }
 
-__global__ void __launch_bounds__(128) k_combine(const G1Xyzz* __restrict__ partial, const uint32_t* __restrict__ ntasks,
-                                                 const uint32_t* __restrict__ toff, uint32_t nbuckets,
-                                                 G1Xyzz* __restrict__ buckets) {
+// bucket b = sum of its partials: chunks first..last that its entry range meets.
+// Buckets met by more than kLongPartials chunks (skewed digits: equal or tiny scalars)
+// are queued for k_combine_long, where a whole CTA adds the partials as a tree.
+constexpr uint32_t kLongPartials = 6;
+constexpr int kLongThreads = 128;
+
+__global__ void __launch_bounds__(128) k_combine(const G1Xyzz* __restrict__ partial, const uint32_t* __restrict__ offsets,
+                                                 uint32_t nbuckets, uint32_t nt, G1Xyzz* __restrict__ buckets,
+                                                 uint32_t* __restrict__ long_list /* [0] = count */) {
     uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nbuckets) return;
-    uint32_t nt = ntasks[b], t0 = toff[b];
+    const uint32_t K = chunk_len(offsets[nbuckets], nt);
+    uint32_t lo = offsets[b], hi = offsets[b + 1];
     G1Xyzz acc = G1Xyzz::inf();
-    if (nt) acc = partial[t0];
-    for (uint32_t k = 1; k < nt; k++) g1_add(acc, partial[t0 + k]);
+    if (hi > lo) {
+        uint32_t t0 = lo / K, t1 = (hi - 1) / K;
+        if (t1 - t0 >= kLongPartials) {
+            long_list[1 + atomicAdd(long_list, 1u)] = b;
+            return;
+        }
+        acc = partial[b + t0];
+        for (uint32_t t = t0 + 1; t <= t1; t++) g1_add(acc, partial[b + t]);
+    }
     buckets[b] = acc;
 }
 
-// Blocked running sums.  For segment s of X (length m, zero-padded):
-//   A = sum_i X[sL+i],  T = sum_i i*X[sL+i]
-// outputs  X'[s] = 2^l * A  (so that S(X) = sum_s T_s + S(X')), and
-//          P'[s] = T + sum_i P[sL+i]   (pending plain sums carried along).
-// Several independent windows are laid out back to back with stride `stride_in`.
-__global__ void __launch_bounds__(128) k_seg_reduce(const G1Xyzz* __restrict__ X, const G1Xyzz* __restrict__ P, uint32_t m,
-                                                    uint32_t stride_in, G1Xyzz* __restrict__ Xo, G1Xyzz* __restrict__ Po,
-                                                    uint32_t mo, uint32_t nwin) {
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= mo * nwin) return;
-    uint32_t w = t / mo, s = t % mo;
-    const G1Xyzz* x = X + (size_t)w * stride_in;
-    const G1Xyzz* p = P ? P + (size_t)w * stride_in : nullptr;
-    uint32_t lo = s << kSegLog;
-    uint32_t hi = lo + kSeg < m ? lo + kSeg : m;
-    G1Xyzz run = G1Xyzz::inf(), acc = G1Xyzz::inf(), pend = G1Xyzz::inf();
-    for (uint32_t i = hi; i > lo; i--) {
-        g1_add(run, x[i - 1]);
-        if (i - 1 > lo) g1_add(acc, run);
-        if (p) g1_add(pend, p[i - 1]);
+__global__ void __launch_bounds__(kLongThreads) k_combine_long(const G1Xyzz* __restrict__ partial,
+                                                               const uint32_t* __restrict__ offsets, uint32_t nbuckets,
+                                                               uint32_t nt, G1Xyzz* __restrict__ buckets,
+                                                               const uint32_t* __restrict__ long_list) {
+    __shared__ G1Xyzz sm[kLongThreads];
+    const uint32_t K = chunk_len(offsets[nbuckets], nt);
+    const uint32_t nlong = long_list[0];
+    for (uint32_t i = blockIdx.x; i < nlong; i += gridDim.x) {
+        const uint32_t b = long_list[1 + i];
+        const uint32_t t0 = offsets[b] / K, t1 = (offsets[b + 1] - 1) / K;
+        G1Xyzz acc = G1Xyzz::inf();
+        for (uint32_t t = t0 + threadIdx.x; t <= t1; t += kLongThreads) g1_add(acc, partial[b + t]);
+        __syncthreads();  // previous round's readers of sm[] are done
+        sm[threadIdx.x] = acc;
+        for (uint32_t s = kLongThreads / 2; s > 0; s >>= 1) {
+            __syncthreads();
+            if (threadIdx.x < s) {
+                G1Xyzz x = sm[threadIdx.x];
+                g1_add(x, sm[threadIdx.x + s]);
+                sm[threadIdx.x] = x;
+            }
+        }
+        if (threadIdx.x == 0) buckets[b] = sm[0];
     }
-    g1_add(pend, acc);
-    for (int d = 0; d < kSegLog; d++) run = g1_dbl(run);
-    Xo[(size_t)w * mo + s] = run;
-    Po[(size_t)w * mo + s] = pend;
 }
 
-// top of the reduction + window combine.  Thread w: S_w = sum_i i*X_w[i] + sum_i P_w[i],
-// scaled by 2^(c*w); thread 0 then adds the nwin results.
-__global__ void k_finish(const G1Xyzz* X, const G1Xyzz* P, uint32_t m, uint32_t nwin, int c, G1Xyzz* out) {
+// ---- bucket reduction  S = sum_i (i+1) * X[i]  over 2^k buckets per set (bucket
+// index = |digit| - 1), organised so that every step is a PLAIN sum with a short
+// dependent chain (an XYZZ addition is ~14 dependent Fp multiplies, ~14 us on one
+// thread, so running-sum schemes are latency-bound):
+//   * k > kDirectBits: write i = hi*2^l + lo.  With row sums R[hi] and column sums
+//     C[lo] of the 2^h x 2^l bucket matrix,
+//         S = sum_lo lo*C[lo] + 2^l * sum_hi hi*R[hi] + sum_hi R[hi]
+//     (2 additions per bucket, done by k_fold passes of <= 3 additions per thread);
+//   * a weighted sum over n <= 2^kDirectBits.. elements is taken bit by bit:
+//         sum_i i*Y[i] = sum_j 2^j * (sum of the Y[i] whose index has bit j set)
+//     one block per (set, bit): strided partial sums + a shared-memory tree (k_bits);
+//   * k_bit_combine scales the per-bit sums by 2^j (j doublings, in parallel) and adds
+//     them with a tree.
+constexpr int kDirectBits = 8;
+
+struct FoldDir {
+    const G1Xyzz* in;
+    G1Xyzz* out;
+    uint32_t n_out;  // outputs of this pass (0: direction idle)
+    uint32_t G;      // inputs per output
+    uint32_t L;      // stride between the inputs of one output (1: contiguous)
+};
+struct FoldArgs {
+    FoldDir d[2];  // [0] row sums, [1] column sums
+};
+
+// out[o] = sum_{g<G} in[(o / L)*G*L + (o % L) + g*L]
+__global__ void __launch_bounds__(128) k_fold(FoldArgs a) {
+    const FoldDir& d = a.d[blockIdx.y];
+    uint32_t o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= d.n_out) return;
+    size_t base = (size_t)(o / d.L) * d.G * d.L + (o % d.L);
+    G1Xyzz acc = d.in[base];
+    for (uint32_t g = 1; g < d.G; g++) g1_add(acc, d.in[base + (size_t)g * d.L]);
+    d.out[o] = acc;
+}
+
+struct BitsArgs {
+    const G1Xyzz* X;  // direct: [set][2^k]
+    const G1Xyzz* C;  // split: [set][2^l] column sums
+    const G1Xyzz* R;  // split: [set][2^h] row sums
+    int k, l, h;      // l == 0: direct
+    G1Xyzz* Q;        // [set][k+1]: per-bit sums by overall weight, Q[k] = plain total
+};
+
+constexpr int kBitsThreads = 128;
+
+__global__ void __launch_bounds__(kBitsThreads) k_bits(BitsArgs a) {
+    __shared__ G1Xyzz sm[kBitsThreads];
+    const uint32_t set = blockIdx.x / (a.k + 1), q = blockIdx.x % (a.k + 1);
+    const G1Xyzz* src;
+    uint32_t n;
+    int bit;  // -1: plain total
+    if (a.l == 0) {
+        src = a.X + ((size_t)set << a.k);
+        n = 1u << a.k;
+        bit = (int)q < a.k ? (int)q : -1;
+    } else if ((int)q < a.l) {
+        src = a.C + ((size_t)set << a.l);
+        n = 1u << a.l;
+        bit = (int)q;
+    } else {
+        src = a.R + ((size_t)set << a.h);
+        n = 1u << a.h;
+        bit = (int)q < a.k ? (int)q - a.l : -1;
+    }
+    const uint32_t cnt = bit < 0 ? n : n >> 1;
+    G1Xyzz acc = G1Xyzz::inf();
+    for (uint32_t i = threadIdx.x; i < cnt; i += kBitsThreads) {
+        uint32_t idx = bit < 0 ? i : (((i >> bit) << (bit + 1)) | (1u << bit) | (i & ((1u << bit) - 1u)));
+        g1_add(acc, src[idx]);
+    }
+    sm[threadIdx.x] = acc;
+    for (uint32_t s = kBitsThreads / 2; s > 0; s >>= 1) {
+        __syncthreads();
+        if (threadIdx.x < s && threadIdx.x + s < cnt) {
+            G1Xyzz x = sm[threadIdx.x];
+            g1_add(x, sm[threadIdx.x + s]);
+            sm[threadIdx.x] = x;
+        }
+    }
+    if (threadIdx.x == 0) a.Q[(size_t)set * (a.k + 1) + q] = sm[0];
+}
+
+// S[set] = sum_{j<k} 2^j * Q[set][j] + Q[set][k].  One block of 32 threads per set.
+__global__ void __launch_bounds__(32) k_bit_combine(const G1Xyzz* __restrict__ Q, int k, G1Xyzz* __restrict__ S) {
+    __shared__ G1Xyzz sm[32];
+    const uint32_t set = blockIdx.x, j = threadIdx.x;
+    G1Xyzz acc = G1Xyzz::inf();
+    if ((int)j <= k) {
+        acc = Q[(size_t)set * (k + 1) + j];
+        if ((int)j < k)
+            for (uint32_t d = 0; d < j; d++) acc = g1_dbl(acc);
+    }
+    sm[j] = acc;
+    for (uint32_t s = 16; s > 0; s >>= 1) {
+        __syncwarp();
+        if (j < s) {
+            G1Xyzz x = sm[j];
+            g1_add(x, sm[j + s]);
+            sm[j] = x;
+        }
+    }
+    if (j == 0) S[set] = sm[0];
+}
+
+// untabulated bases: out = sum_w 2^(c*w) * S[w] (thread w doubles c*w times, thread 0 adds)
+__global__ void __launch_bounds__(64) k_window_combine(const G1Xyzz* __restrict__ S, uint32_t nwin, int c, G1Xyzz* __restrict__ out) {
     __shared__ G1Xyzz part[64];
     uint32_t w = threadIdx.x;
-    X += (size_t)blockIdx.x * nwin * m;  // one block per output (batch row)
-    if (P) P += (size_t)blockIdx.x * nwin * m;
-    out += blockIdx.x;
+    S += (size_t)blockIdx.x * nwin;  // one block per output (batch row)
     if (w < nwin) {
-        const G1Xyzz* x = X + (size_t)w * m;
-        G1Xyzz run = G1Xyzz::inf(), acc = G1Xyzz::inf();
-        for (uint32_t i = m; i > 1; i--) {
-            g1_add(run, x[i - 1]);
-            g1_add(acc, run);
-        }
-        if (P)
-            for (uint32_t i = 0; i < m; i++) g1_add(acc, P[(size_t)w * m + i]);
+        G1Xyzz acc = S[w];
         for (uint32_t d = 0; d < (uint32_t)c * w; d++) acc = g1_dbl(acc);
         part[w] = acc;
     }
@@ -255,7 +379,7 @@ __global__ void k_finish(const G1Xyzz* X, const G1Xyzz* P, uint32_t m, uint32_t 
     if (w == 0) {
         G1Xyzz total = part[0];
         for (uint32_t i = 1; i < nwin; i++) g1_add(total, part[i]);
-        *out = total;
+        out[blockIdx.x] = total;
     }
 }
 
@@ -297,6 +421,8 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
 
 }  // namespace
 
+int msm_num_windows(int c) { return (255 + c - 1) / c; }  // scalars are recoded below 2^254 (k_digits)
+
 int msm_pick_window(size_t n, bool tabulated) {
     int lg = 0;
     while (((size_t)1 << (lg + 1)) <= n) lg++;
@@ -337,24 +463,25 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     const size_t n = len * batch;
     const bool tab = bases.c > 0;
     const int c = tab ? bases.c : msm_pick_window(len, false);
-    const int nwin = (256 + c - 1) / c;
+    const int nwin = msm_num_windows(c);
     if (tab && nwin != bases.nwin) throw CudaError{"msm: table window count mismatch"};
     // with a table the entries index [w][k] over the FULL resident row length
     if ((uint64_t)(tab ? nwin : 1) * bases.n * batch >= (1ull << 31) || n >= (1ull << 32)) throw CudaError{"msm: index space exceeds 31 bits"};
-    const uint32_t bpw = (1u << (c - 1)) + 1;         // bucket index = |digit|, 0 unused
-    const uint32_t bpw_pad = (bpw + kSeg - 1) / kSeg * kSeg;
+    const int k = c - 1;                                // buckets per set = 2^k, index = |digit| - 1
+    const uint32_t bpw = 1u << k;
     const uint32_t per_out = tab ? 1u : (uint32_t)nwin;  // bucket sets per output
     const uint32_t nsets = per_out * (uint32_t)batch;
-    const uint32_t nbuckets = nsets * bpw_pad;
+    if ((uint64_t)nsets * bpw >= (1ull << 31)) throw CudaError{"msm: too many buckets"};
+    const uint32_t nbuckets = nsets * bpw;
 
-    uint32_t* counts = s.counts.as<uint32_t>(nbuckets);
-    uint32_t* offsets = s.offsets.as<uint32_t>(nbuckets);
-    uint32_t* cursor = s.cursor.as<uint32_t>(nbuckets);
+    uint32_t* counts = s.counts.as<uint32_t>(nbuckets + 1);
+    uint32_t* offsets = s.offsets.as<uint32_t>(nbuckets + 1);  // offsets[nbuckets] = number of entries
+    uint32_t* cursor = s.cursor.as<uint32_t>(nbuckets + 1);
     uint32_t* sorted = s.sorted.as<uint32_t>((size_t)n * nwin);
     G1Xyzz* buckets = s.buckets.as<G1Xyzz>(nbuckets);
 
     prof_mark("msm.digits_count", st);
-    FB_CUDA(cudaMemsetAsync(counts, 0, nbuckets * sizeof(uint32_t), st));
+    FB_CUDA(cudaMemsetAsync(counts, 0, (nbuckets + 1) * sizeof(uint32_t), st));
     DigitArgs a;
     a.scalars = d_scalars;
     a.n = (uint32_t)n;
@@ -364,57 +491,97 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     a.nwin = nwin;
     a.mont = scalars_mont ? 1 : 0;
     a.tabulated = tab ? 1 : 0;
-    a.buckets_per_win = bpw_pad;
+    a.buckets_per_win = bpw;
     a.counts = counts;
     a.sorted = sorted;
     DigitArgs a2 = a;
     const unsigned gb = (unsigned)((n + 255) / 256);
     (++fb::g_launches, k_digits<false><<<gb, 256, 0, st>>>(a));
     prof_mark("msm.scan", st);
-    exclusive_scan(counts, offsets, nbuckets, s.block_sums, st);
+    exclusive_scan(counts, offsets, nbuckets + 1, s.block_sums, st);
     FB_CUDA(cudaMemcpyAsync(cursor, offsets, nbuckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     a2.counts = cursor;
     prof_mark("msm.scatter", st);
     (++fb::g_launches, k_digits<true><<<gb, 256, 0, st>>>(a2));
-    prof_mark("msm.tasks", st);
-    const uint64_t entries = (uint64_t)n * nwin;
-    uint32_t cap = (uint32_t)(2 * entries / nbuckets);
-    if (cap < 32) cap = 32;
-    if (cap > 512) cap = 512;
-    const uint32_t max_tasks = nbuckets + (uint32_t)(entries / cap) + 1;
-    uint32_t* ntasks = s.order.as<uint32_t>((size_t)2 * nbuckets + 4);
-    uint32_t* toff = ntasks + nbuckets;
-    uint32_t* d_total = toff + nbuckets;
-    uint2* tasks = s.misc.as<uint2>(max_tasks);
-    G1Xyzz* partial = s.seg_t.as<G1Xyzz>(max_tasks);
-    (++fb::g_launches, k_task_count<<<(nbuckets + 255) / 256, 256, 0, st>>>(counts, nbuckets, cap, ntasks));
-    exclusive_scan(ntasks, toff, nbuckets, s.block_sums, st);
-    (++fb::g_launches, k_task_fill<<<(nbuckets + 255) / 256, 256, 0, st>>>(counts, offsets, ntasks, toff, nbuckets, tasks, d_total));
+
+    // accumulate: one wave of resident threads, equal chunks of the sorted entries
     prof_mark("msm.accumulate", st);
-    (++fb::g_launches, k_accumulate<<<(max_tasks + 127) / 128, 128, 0, st>>>(bases.pts, sorted, tasks, d_total, partial));
+    static int acc_blocks_per_sm = 0;
+    if (!acc_blocks_per_sm) {
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate, 128, 0));
+        if (acc_blocks_per_sm < 1) acc_blocks_per_sm = 1;
+    }
+    const uint64_t entries = (uint64_t)n * nwin;
+    uint32_t acc_blocks = (uint32_t)(kNumSMs * acc_blocks_per_sm);
+    {   // small inputs: no more threads than chunks of kMinChunk entries
+        uint64_t need = (entries / kMinChunk + 127) / 128 + 1;
+        if (need < acc_blocks) acc_blocks = (uint32_t)need;
+    }
+    const uint32_t nt = acc_blocks * 128;
+    G1Xyzz* partial = s.seg_t.as<G1Xyzz>((size_t)nbuckets + nt);
+    (++fb::g_launches, k_accumulate<<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
     prof_mark("msm.combine", st);
-    (++fb::g_launches, k_combine<<<(nbuckets + 127) / 128, 128, 0, st>>>(partial, ntasks, toff, nbuckets, buckets));
+    uint32_t* long_list = s.order.as<uint32_t>((size_t)nt + 2);
+    FB_CUDA(cudaMemsetAsync(long_list, 0, sizeof(uint32_t), st));
+    (++fb::g_launches, k_combine<<<(nbuckets + 127) / 128, 128, 0, st>>>(partial, offsets, nbuckets, nt, buckets, long_list));
+    (++fb::g_launches, k_combine_long<<<2 * kNumSMs, kLongThreads, 0, st>>>(partial, offsets, nbuckets, nt, buckets, long_list));
 
     // bucket reduction
     prof_mark("msm.reduce", st);
-    const G1Xyzz* X = buckets;
-    const G1Xyzz* P = nullptr;
-    uint32_t m = bpw_pad;
-    G1Xyzz* seg = s.seg_a.as<G1Xyzz>((size_t)4 * nsets * ((bpw_pad >> kSegLog) + kSeg));
-    size_t seg_off = 0;
-    while (m > kSeg) {
-        uint32_t mo = (m + kSeg - 1) >> kSegLog;
-        G1Xyzz* Xo = seg + seg_off;
-        G1Xyzz* Po = Xo + (size_t)nsets * mo;
-        seg_off += (size_t)2 * nsets * mo;
-        uint32_t threads = mo * nsets;
-        (++fb::g_launches, k_seg_reduce<<<(threads + 127) / 128, 128, 0, st>>>(X, P, m, m, Xo, Po, mo, nsets));
-        X = Xo;
-        P = Po;
-        m = mo;
+    BitsArgs ba;
+    ba.X = buckets;
+    ba.C = ba.R = nullptr;
+    ba.k = k;
+    ba.l = ba.h = 0;
+    if (k > kDirectBits) {
+        const int l = (k + 1) / 2, h = k - l;
+        // ping-pong arenas: every pass shrinks its input by >= 2
+        G1Xyzz* arena = s.seg_a.as<G1Xyzz>((size_t)2 * nbuckets);
+        G1Xyzz* row_buf[2] = {arena, arena + nbuckets / 2};
+        G1Xyzz* col_buf[2] = {arena + nbuckets, arena + nbuckets + nbuckets / 2};
+        const G1Xyzz* rin = buckets;
+        const G1Xyzz* cin = buckets;
+        uint32_t rl = 1u << l;  // remaining row length (row sums shrink it to 1)
+        uint32_t ch = 1u << h;  // remaining column height
+        int pp = 0;
+        while (rl > 1 || ch > 1) {
+            FoldArgs fa;
+            fa.d[0] = FoldDir{rin, row_buf[pp], 0, 1, 1};
+            fa.d[1] = FoldDir{cin, col_buf[pp], 0, 1, 1};
+            uint32_t mx = 0;
+            if (rl > 1) {
+                uint32_t G = rl >= 4 ? 4 : 2;
+                rl /= G;
+                fa.d[0].G = G;
+                fa.d[0].L = 1;
+                fa.d[0].n_out = nsets * (1u << h) * rl;
+                rin = row_buf[pp];
+                mx = fa.d[0].n_out;
+            }
+            if (ch > 1) {
+                uint32_t G = ch >= 4 ? 4 : 2;
+                ch /= G;
+                fa.d[1].G = G;
+                fa.d[1].L = 1u << l;
+                fa.d[1].n_out = nsets * ch * (1u << l);
+                cin = col_buf[pp];
+                if (fa.d[1].n_out > mx) mx = fa.d[1].n_out;
+            }
+            (++fb::g_launches, k_fold<<<dim3((mx + 127) / 128, 2), 128, 0, st>>>(fa));
+            pp ^= 1;
+        }
+        ba.R = rin;
+        ba.C = cin;
+        ba.l = l;
+        ba.h = h;
     }
+    G1Xyzz* Q = s.misc.as<G1Xyzz>((size_t)nsets * (k + 1) + nsets);
+    G1Xyzz* S = Q + (size_t)nsets * (k + 1);
+    ba.Q = Q;
+    (++fb::g_launches, k_bits<<<nsets * (k + 1), kBitsThreads, 0, st>>>(ba));
     prof_mark("msm.finish", st);
-    (++fb::g_launches, k_finish<<<(unsigned)batch, 64, 0, st>>>(X, P, m, per_out, c, d_out));
+    (++fb::g_launches, k_bit_combine<<<nsets, 32, 0, st>>>(Q, k, tab ? d_out : S));
+    if (!tab) (++fb::g_launches, k_window_combine<<<(unsigned)batch, 64, 0, st>>>(S, (uint32_t)nwin, c, d_out));
     prof_mark("post", st);
     FB_CUDA(cudaGetLastError());
 }

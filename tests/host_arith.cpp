@@ -40,7 +40,7 @@ void h_fp_mul_portable(const uint32_t* a, const uint32_t* b, uint32_t* r) {
     Fp z = fe_mul_portable<FpParams>(x, y);
     memcpy(r, z.v, 48);
 }
-// op: 0 add, 1 sub, 2 neg(a), 3 inv(a), 4 to_mont(a), 5 from_mont(a)
+// op: 0 add, 1 sub, 2 neg(a), 3 inv(a), 4 to_mont(a), 5 from_mont(a), 6 inv_gcd(a)
 void h_fr_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
     Fr x, y, z;
     memcpy(x.v, a, 32);
@@ -51,6 +51,7 @@ void h_fr_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
         case 2: z = fe_neg<FrParams>(x); break;
         case 3: z = fe_inv<FrParams>(x); break;
         case 4: z = fe_to_mont<FrParams>(x); break;
+        case 6: z = fe_inv_gcd<FrParams>(x); break;
         default: z = fe_from_mont<FrParams>(x); break;
     }
     memcpy(r, z.v, 32);
@@ -65,6 +66,7 @@ void h_fp_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
         case 2: z = fe_neg<FpParams>(x); break;
         case 3: z = fe_inv<FpParams>(x); break;
         case 4: z = fe_to_mont<FpParams>(x); break;
+        case 6: z = fe_inv_gcd<FpParams>(x); break;
         default: z = fe_from_mont<FpParams>(x); break;
     }
     memcpy(r, z.v, 48);

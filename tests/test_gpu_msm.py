@@ -63,6 +63,9 @@ def test_msm_edge_scalars_and_points(be, tab, c):
     ks[7] = 1
     ks[8] = (1 << 255) % R
     ks[9] = (1 << 254) - 1
+    ks[10] = (R - 1) // 2  # largest scalar kept as is by the signed recoding
+    ks[11] = (R + 1) // 2  # smallest scalar recoded as -(r - k)
+    ks[12] = (1 << 254)
     bases = be.bases_from_scalars(ss)
     if tab:
         bases.precompute(c)
@@ -124,4 +127,21 @@ def test_msm_large_known_dlog(be, log_n, tab):
     ss = synth.fr_ints(21, n)
     ks = synth.fr_ints(22, n)
     assert got == expect(ss, ks)
+    bases.free()
+
+
+@pytest.mark.parametrize("tab", [False, True])
+def test_msm_skewed_large(be, tab):
+    """Hot buckets: equal, tiny and two-valued scalars put tens of thousands of points
+    into a handful of buckets (the chunked accumulation + tree combine path)."""
+    from fourier_b200 import synth
+    n = 1 << 16
+    sb = synth.fr_bytes(23, n)
+    ss = synth.fr_ints(23, n)
+    bases = be.bases_from_scalars(sb)
+    if tab:
+        bases.precompute()
+    for ks in ([7] * n, [i % 3 for i in range(n)], [R - 1 if i & 1 else (R + 1) // 2 for i in range(n)],
+               [(i * i) % 1000 for i in range(n)]):
+        assert be.msm(bases, ks) == expect(ss, ks)
     bases.free()

@@ -63,6 +63,10 @@ def test_field_ops(L, name, m, n):
         assert val(r) == a * RR % m
         op(5, arr(a, n), arr(b, n), r)
         assert val(r) == a * Ri % m
+    # binary-GCD inversion (the single-result XYZZ -> affine path) == Fermat == big-int
+    for a, b in cases[:600] + [(k, 0) for k in (2, 3, m - 2, (m - 1) // 2, (m + 1) // 2)]:
+        op(6, arr(a, n), arr(b, n), r)
+        assert val(r) == (pow(a * Ri % m, -1, m) * RR % m if a else 0)
 
 
 def cb(b):
