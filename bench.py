@@ -271,8 +271,8 @@ def own_arm(args):
     if rank == 0:
         peaks = load_peaks()
         int_peak, int_src = load_int_peak()
-        lg = max(ncols.bit_length() - 1, 1)
-        wbits = WINDOW if WINDOW else max(4, min(20, lg - 1))   # msm_pick_window(tabulated)
+        nw = lambda c: (255 + c - 1) // c
+        wbits = WINDOW if WINDOW else min(range(4, 23), key=lambda c: ncols * nw(c) * 10 + (1 << (c - 1)) * 28)  # msm_pick_window
         table_windows = (255 + wbits - 1) // wbits
         acc_ms, acc_cnt = prof.get("msm.accumulate", (0.0, 1))
         acc_avg_s = acc_ms / max(acc_cnt, 1) * 1e-3

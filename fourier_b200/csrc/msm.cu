@@ -18,6 +18,8 @@
 //   5. k_fold / k_bits / k_bit_combine: sum_i (i+1)*B_i as row + column sums of the
 //      bucket matrix and bit-sliced weighted sums (plain sums only, short chains)
 //   6. k_window_combine: per-window results (doubling ladder) when not tabulated
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace fb {
@@ -170,9 +172,10 @@ __device__ __forceinline__ uint32_t chunk_len(uint32_t E, uint32_t nt) {
     return k < kMinChunk ? kMinChunk : k;
 }
 
-__global__ void __launch_bounds__(128) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
-                                                    const uint32_t* __restrict__ offsets, uint32_t nbuckets,
-                                                    G1Xyzz* __restrict__ partial) {
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
+                                                          const uint32_t* __restrict__ offsets, uint32_t nbuckets,
+                                                          G1Xyzz* __restrict__ partial) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t E = offsets[nbuckets];
     const uint32_t K = chunk_len(E, gridDim.x * blockDim.x);
@@ -286,7 +289,7 @@ struct FoldArgs {
 };
 
 // out[o] = sum_{g<G} in[(o / L)*G*L + (o % L) + g*L]
-__global__ void __launch_bounds__(128) k_fold(FoldArgs a) {
+__global__ void __launch_bounds__(128, 3) k_fold(FoldArgs a) {
     const FoldDir& d = a.d[blockIdx.y];
     uint32_t o = blockIdx.x * blockDim.x + threadIdx.x;
     if (o >= d.n_out) return;
@@ -423,15 +426,23 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
 
 int msm_num_windows(int c) { return (255 + c - 1) / c; }  // scalars are recoded below 2^254 (k_digits)
 
+// Window width by a cost model in Fp multiplications: n*W mixed additions (10 each)
+// plus 2 full additions (14 each) per bucket; without a table every window has its own
+// bucket set and the windows are joined by a doubling ladder.
 int msm_pick_window(size_t n, bool tabulated) {
-    int lg = 0;
-    while (((size_t)1 << (lg + 1)) <= n) lg++;
-    int c;
-    if (tabulated) c = lg - 1;  // one bucket set shared by all windows
-    else c = lg - 4;
-    if (c < 4) c = 4;
-    if (c > 20) c = 20;
-    return c;
+    int best = 4;
+    double best_cost = 1e300;
+    for (int c = 4; c <= 22; c++) {
+        const double W = (double)msm_num_windows(c);
+        const double buckets = (double)((size_t)1 << (c - 1)) * (tabulated ? 1.0 : W);
+        double cost = (double)n * W * 10.0 + buckets * 28.0;
+        if (!tabulated) cost += 255.0 * 9.0;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = c;
+        }
+    }
+    return best;
 }
 
 void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, G1Affine* d_out, DevBuf& scratch,
@@ -506,9 +517,12 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
 
     // accumulate: one wave of resident threads, equal chunks of the sorted entries
     prof_mark("msm.accumulate", st);
-    static int acc_blocks_per_sm = 0;
+    static int acc_blocks_per_sm = 0, acc_minb = 4;  // 4 blocks/SM (128 registers, 16 warps): measured 5% faster than 3
     if (!acc_blocks_per_sm) {
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate, 128, 0));
+        const char* e = getenv("FB_ACC_MINB");  // tuning knob
+        if (e && atoi(e) == 3) acc_minb = 3;
+        if (acc_minb == 4) FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate<4>, 128, 0));
+        else FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate<3>, 128, 0));
         if (acc_blocks_per_sm < 1) acc_blocks_per_sm = 1;
     }
     const uint64_t entries = (uint64_t)n * nwin;
@@ -519,7 +533,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     }
     const uint32_t nt = acc_blocks * 128;
     G1Xyzz* partial = s.seg_t.as<G1Xyzz>((size_t)nbuckets + nt);
-    (++fb::g_launches, k_accumulate<<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
+    if (acc_minb == 4) (++fb::g_launches, k_accumulate<4><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
+    else (++fb::g_launches, k_accumulate<3><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
     prof_mark("msm.combine", st);
     uint32_t* long_list = s.order.as<uint32_t>((size_t)nt + 2);
     FB_CUDA(cudaMemsetAsync(long_list, 0, sizeof(uint32_t), st));
