@@ -4,7 +4,7 @@ NVCC      ?= nvcc
 CXX       ?= g++
 CC        := /usr/bin/gcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2 --expt-relaxed-constexpr -Xptxas -v
+NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2 --expt-relaxed-constexpr -Xptxas -v $(EXTRA_NVFLAGS)
 CSRC      := fourier_b200/csrc
 BUILD     := build
 CU        := ntt poly msm g1ops srs api engine

@@ -111,7 +111,8 @@ void fb_ctx_destroy(fb_ctx* c) {
     if (c->y_bases.pts && c->y_bases.pts != c->d_g_tau_y) cudaFree(c->y_bases.pts);
     if (c->d_u) cudaFree(c->d_u);
     DevBuf* bufs[] = {&c->msm.counts, &c->msm.offsets, &c->msm.cursor, &c->msm.sorted, &c->msm.buckets, &c->msm.block_sums,
-                      &c->msm.seg_a, &c->msm.seg_t, &c->msm.order, &c->msm.misc, &c->in_bytes, &c->fr_a, &c->fr_b, &c->fr_c,
+                      &c->msm.seg_a, &c->msm.seg_t, &c->msm.order, &c->msm.misc, &c->msm.pts_a, &c->msm.pts_b, &c->msm.pref,
+                      &c->msm.where, &c->in_bytes, &c->fr_a, &c->fr_b, &c->fr_c,
                       &c->pt_a, &c->pt_b, &c->out_bytes, &c->scan, &c->small, &c->eng_a, &c->eng_b};
     for (DevBuf* b : bufs) b->release();
     if (c->d_err) cudaFree(c->d_err);

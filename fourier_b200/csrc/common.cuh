@@ -125,7 +125,7 @@ struct MsmBases {
 };
 
 struct MsmScratch {
-    DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc;
+    DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc, pts_a, pts_b, pref, where;
 };
 
 // d_out[b] (device XYZZ) = sum_k scalars[b*len + k] * bases_b[k] for b < batch, where

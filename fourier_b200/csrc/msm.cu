@@ -155,6 +155,211 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
     return r;
 }
 
+// ---- batched-affine halving rounds.  A mixed XYZZ addition costs 10 Fp multiplies;
+// an AFFINE addition costs 3 once 1/(x2 - x1) is known, and Montgomery's trick turns
+// P inversions into one inversion plus 3(P-1) multiplies.  One round replaces every
+// bucket's points (p0, p1, p2, ...) by (p0+p1, p2+p3, ...): 6 multiplies per addition.
+// Each thread owns P consecutive OUTPUT slots of the round:
+//   pass 1  walks its slots, forms the denominator of each pair (x2 - x1; 2*y for a
+//           doubling; 1 when nothing is to be inverted) and parks the running product
+//           in scratch (slot-major, so a warp writes consecutive elements);
+//   warp    the 32 per-thread products are multiplied together with shuffles, ONE
+//           lane inverts the product (binary GCD, no multiplies) and every lane
+//           recovers the inverse of its own product from the prefix/suffix products;
+//   pass 2  walks the slots backwards, peels off each pair's inverse and writes the sum.
+// After a few rounds the survivors (a few per bucket) go through the XYZZ kernel below.
+struct RoundArgs {
+    const G1Affine* pts;      // FIRST: the resident table (gathered through `sorted`); else the previous round's output
+    const uint32_t* sorted;   // FIRST only: table index | sign << 31
+    const uint32_t* off_in;   // [nbuckets + 1] bucket offsets of the input
+    const uint32_t* off_out;  // [nbuckets + 1] bucket offsets of the output, off_out[b+1]-off_out[b] = ceil(count_in/2)
+    uint32_t nbuckets;
+    G1Affine* out;
+    Fp* pref;                 // [slot][thread] running products
+    uint32_t* where;          // [slot][thread] first input index of the slot | (has a second point) << 31
+    uint32_t p_max;           // slots per thread the scratch was sized for
+    uint64_t dbg_in, dbg_out, dbg_tab;  // element counts of the input / output / table arrays (bounds checks)
+};
+
+constexpr uint32_t kMinSlots = 16;
+
+template <bool FIRST>
+__device__ __forceinline__ G1Affine round_load(const RoundArgs& a, uint32_t e) {
+#ifdef FB_DEBUG_BOUNDS
+    if (e >= a.dbg_in) { printf("round_load: e=%u >= in=%llu (first=%d)\n", e, (unsigned long long)a.dbg_in, (int)FIRST); return G1Affine::inf(); }
+    if (FIRST && (a.sorted[e] & 0x7fffffffu) >= a.dbg_tab) { printf("round_load: ent=%u >= tab=%llu\n", a.sorted[e] & 0x7fffffffu, (unsigned long long)a.dbg_tab); return G1Affine::inf(); }
+#endif
+    if (FIRST) {
+        uint32_t ent = a.sorted[e];
+        G1Affine p = ldg_affine(a.pts + (ent & 0x7fffffffu));
+        if ((ent >> 31) && !p.is_inf()) p.y = fe_neg<FpParams>(p.y);
+        return p;
+    }
+    return ldg_affine(a.pts + e);
+}
+
+// kind of a slot: 0 result = p1, 1 result = p2, 2 generic sum, 3 doubling, 4 identity
+__device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2, bool has2, Fp& den) {
+    using F = FpParams;
+    den = Fp::one();
+    if (!has2 || p2.is_inf()) return 0;
+    if (p1.is_inf()) return 1;
+    Fp dx = fe_sub<F>(p2.x, p1.x);
+    if (!dx.is_zero()) {
+        den = dx;
+        return 2;
+    }
+    if (p1.y == p2.y) {  // y != 0: the curve has no point of order 2
+        den = fe_dbl<F>(p1.y);
+        return 3;
+    }
+    return 4;
+}
+
+__device__ __forceinline__ Fp shfl_fp(const Fp& v, int src) {
+    Fp r;
+#pragma unroll
+    for (int i = 0; i < 12; i++) r.v[i] = __shfl_sync(0xffffffffu, v.v[i], src);
+    return r;
+}
+
+// every lane passes its product t (non-zero) and gets 1/t; one inversion per warp
+__device__ __forceinline__ Fp warp_batch_inverse(const Fp& t) {
+    using F = FpParams;
+    const int lane = threadIdx.x & 31;
+    Fp pre = t, suf = t;  // inclusive prefix / suffix products
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Fp up = shfl_fp(pre, lane - d < 0 ? lane : lane - d);
+        Fp dn = shfl_fp(suf, lane + d > 31 ? lane : lane + d);
+        if (lane >= d) pre = fe_mul<F>(pre, up);
+        if (lane + d <= 31) suf = fe_mul<F>(suf, dn);
+    }
+    Fp inv_total = Fp::zero();
+    if (lane == 31) inv_total = fe_inv_gcd<F>(pre);
+    inv_total = shfl_fp(inv_total, 31);
+    Fp ex_pre = shfl_fp(pre, lane == 0 ? 0 : lane - 1);   // product of the lanes below
+    Fp ex_suf = shfl_fp(suf, lane == 31 ? 31 : lane + 1);  // product of the lanes above
+    Fp r = inv_total;
+    if (lane > 0) r = fe_mul<F>(r, ex_pre);
+    if (lane < 31) r = fe_mul<F>(r, ex_suf);
+    return r;
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(128, 4) k_affine_round(RoundArgs a) {
+    using F = FpParams;
+    const uint32_t nt = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t O = a.off_out[a.nbuckets];
+    uint32_t P = (O + nt - 1) / nt;
+    if (P < kMinSlots) P = kMinSlots;
+    if (P > a.p_max) P = a.p_max;  // cannot happen: p_max comes from an upper bound on O
+    const uint64_t o0 = (uint64_t)t * P;
+    // NB: written as min(O - o0, P) ptxas 12.9 (sm_100a) fuses the subtraction and the min into
+    // VIADDMNMX.U32 with the operand's negation dropped (observed on B200: cnt == P for the last
+    // thread); the empty asm keeps the two apart.
+    uint32_t rem = o0 >= O ? 0u : O - (uint32_t)o0;
+    asm volatile("" : "+r"(rem));
+    const uint32_t cnt = rem < P ? rem : P;
+    if (__ballot_sync(0xffffffffu, cnt != 0) == 0) return;  // whole warp idle
+#ifdef FB_DEBUG_BOUNDS
+    if (t == 0) printf("k_affine_round first=%d O=%u nt=%u P=%u p_max=%u in=%llu out=%llu\n", (int)FIRST, O, nt, P, a.p_max, (unsigned long long)a.dbg_in, (unsigned long long)a.dbg_out);
+    if (O > a.dbg_out) { if (t == 0) printf("O exceeds out capacity\n"); return; }
+    if (t == 0 && a.nbuckets <= 4096) {
+        printf("  off_in=%p off_out=%p in[0..4]=%u %u %u %u %u out[0..4]=%u %u %u %u %u in[nb]=%u\n", a.off_in, a.off_out, a.off_in[0], a.off_in[1], a.off_in[2], a.off_in[3], a.off_in[4],
+               a.off_out[0], a.off_out[1], a.off_out[2], a.off_out[3], a.off_out[4], a.off_in[a.nbuckets]);
+        for (uint32_t b = 0; b < a.nbuckets; b++) {
+            uint32_t ci = a.off_in[b + 1] - a.off_in[b], co = a.off_out[b + 1] - a.off_out[b];
+            if (co != (ci + 1) / 2) { printf("  bucket %u: in %u..%u out %u..%u\n", b, a.off_in[b], a.off_in[b + 1], a.off_out[b], a.off_out[b + 1]); break; }
+        }
+    }
+#endif
+
+    // ---- pass 1
+    Fp run = Fp::one();
+    if (cnt) {
+        uint32_t o = (uint32_t)o0;
+        uint32_t lo = 0, hi = a.nbuckets;  // off_out[lo] <= o < off_out[hi]
+        while (hi - lo > 1) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (a.off_out[mid] <= o) lo = mid;
+            else hi = mid;
+        }
+        uint32_t b = lo;
+        uint32_t ob = a.off_out[b], ob_next = a.off_out[b + 1];
+        uint32_t ib = a.off_in[b], ib_end = a.off_in[b + 1];
+        for (uint32_t j = 0; j < cnt; j++, o++) {
+            if (o == ob_next) {
+                do {
+                    b++;
+                    ob_next = a.off_out[b + 1];
+                } while (ob_next <= o);
+                ob = a.off_out[b];
+                ib = a.off_in[b];
+                ib_end = a.off_in[b + 1];
+            }
+            const uint32_t e = ib + 2 * (o - ob);
+            const bool has2 = e + 1 < ib_end;
+#ifdef FB_DEBUG_BOUNDS
+            if (e >= a.dbg_in) printf("pass1 t=%u o0=%u cnt=%u j=%u o=%u O=%u b=%u ob=%u ob_next=%u ib=%u ib_end=%u\n", t, (uint32_t)o0, cnt, j, o, O, b, ob, ob_next, ib, ib_end);
+#endif
+            G1Affine p1 = round_load<FIRST>(a, e);
+            G1Affine p2 = has2 ? round_load<FIRST>(a, e + 1) : G1Affine::inf();
+            Fp den;
+            (void)pair_kind(p1, p2, has2, den);
+            run = fe_mul<F>(run, den);
+            a.pref[(size_t)j * nt + t] = run;
+            a.where[(size_t)j * nt + t] = e | (has2 ? 0x80000000u : 0u);
+        }
+    }
+    // ---- one inversion per warp
+    Fp inv = warp_batch_inverse(run);
+    // ---- pass 2
+    for (uint32_t j = cnt; j-- > 0;) {
+        const uint32_t w = a.where[(size_t)j * nt + t];
+        const uint32_t e = w & 0x7fffffffu;
+        const bool has2 = (w >> 31) != 0;
+        G1Affine p1 = round_load<FIRST>(a, e);
+        G1Affine p2 = has2 ? round_load<FIRST>(a, e + 1) : G1Affine::inf();
+        Fp den;
+        const int kind = pair_kind(p1, p2, has2, den);
+        Fp dinv = inv;
+        if (j) dinv = fe_mul<F>(inv, a.pref[(size_t)(j - 1) * nt + t]);
+        inv = fe_mul<F>(inv, den);
+        G1Affine r;
+        if (kind == 0) r = p1;
+        else if (kind == 1) r = p2;
+        else if (kind == 4) r = G1Affine::inf();
+        else {
+            Fp num;
+            if (kind == 2) num = fe_sub<F>(p2.y, p1.y);
+            else {
+                Fp xx = fe_sqr<F>(p1.x);
+                num = fe_add<F>(fe_dbl<F>(xx), xx);
+            }
+            Fp lam = fe_mul<F>(num, dinv);
+            Fp x3 = fe_sub<F>(fe_sub<F>(fe_sqr<F>(lam), p1.x), p2.x);
+            Fp y3 = fe_sub<F>(fe_mul<F>(lam, fe_sub<F>(p1.x, x3)), p1.y);
+            r.x = x3;
+            r.y = y3;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(a.out + ((uint32_t)o0 + j));
+#pragma unroll
+        for (int i = 0; i < 3; i++) dst[i] = make_uint4(r.x.v[4 * i], r.x.v[4 * i + 1], r.x.v[4 * i + 2], r.x.v[4 * i + 3]);
+#pragma unroll
+        for (int i = 0; i < 3; i++) dst[3 + i] = make_uint4(r.y.v[4 * i], r.y.v[4 * i + 1], r.y.v[4 * i + 2], r.y.v[4 * i + 3]);
+    }
+}
+
+// counts of the next round: ceil(count/2) per bucket (entry nbuckets = 0 closes the scan)
+__global__ void __launch_bounds__(256) k_halve_counts(const uint32_t* __restrict__ off_in, uint32_t nbuckets,
+                                                      uint32_t* __restrict__ cnt_out) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nbuckets) return;
+    cnt_out[b] = b < nbuckets ? (off_in[b + 1] - off_in[b] + 1) >> 1 : 0u;
+}
+
 // ---- balanced bucket accumulation.  The sorted entry list (E entries, grouped by
 // bucket) is cut into NT equal chunks of K = ceil(E / NT) entries, NT = one wave of
 // resident threads (a multiple of the SM count), whatever the bucket boundaries are:
@@ -172,7 +377,7 @@ __device__ __forceinline__ uint32_t chunk_len(uint32_t E, uint32_t nt) {
     return k < kMinChunk ? kMinChunk : k;
 }
 
-template <int MINB>
+template <int MINB, bool DIRECT>  // DIRECT: pts[e] is entry e itself (output of the affine rounds), no gather, no sign
 __global__ void __launch_bounds__(128, MINB) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
                                                           const uint32_t* __restrict__ offsets, uint32_t nbuckets,
                                                           G1Xyzz* __restrict__ partial) {
@@ -202,9 +407,14 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate(const G1Affine* __rest
                 next = offsets[cb + 1];
             } while (next <= e);
         }
-        uint32_t ent = sorted[e];
-        G1Affine p = ldg_affine(pts + (ent & 0x7fffffffu));
-        if (ent >> 31) p.y = fe_neg<FpParams>(p.y);
+        G1Affine p;
+        if (DIRECT) {
+            p = ldg_affine(pts + e);
+        } else {
+            uint32_t ent = sorted[e];
+            p = ldg_affine(pts + (ent & 0x7fffffffu));
+            if (ent >> 31) p.y = fe_neg<FpParams>(p.y);
+        }
         g1_add_mixed(acc, p);
     }
     partial[cb + t] = acc;
@@ -515,31 +725,82 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     prof_mark("msm.scatter", st);
     (++fb::g_launches, k_digits<true><<<gb, 256, 0, st>>>(a2));
 
-    // accumulate: one wave of resident threads, equal chunks of the sorted entries
+    // batched-affine halving rounds, then XYZZ accumulation of the survivors
+    const uint64_t entries = (uint64_t)n * nwin;
+    static int rounds_env = -2, round_blocks_per_sm = 0;
+    if (rounds_env == -2) {
+        const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
+        rounds_env = e ? atoi(e) : -1;
+        int b0 = 0, b1 = 0;
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_affine_round<true>, 128, 0));
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_affine_round<false>, 128, 0));
+        round_blocks_per_sm = b0 < b1 ? b0 : b1;
+        if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
+    }
+    int rounds = 0;
+    if (rounds_env >= 0) rounds = rounds_env;
+    else
+        while (rounds < 8 && (entries >> rounds) >= 1500000 && ((entries / nbuckets) >> rounds) >= 2) rounds++;
+    const uint32_t* off_cur = offsets;
+    const G1Affine* pts_cur = bases.pts;
+    uint64_t ub = entries;  // upper bound on the number of live points
+    if (rounds > 0) prof_mark("msm.affine_rounds", st);
+    for (int r = 0; r < rounds; r++) {
+        const uint64_t ub_out = (ub + nbuckets) / 2 + 1;
+        uint32_t* cnt_tmp = s.order.as<uint32_t>(nbuckets + 1);
+        uint32_t* off_out = (r & 1) ? cursor : counts;
+        (++fb::g_launches, k_halve_counts<<<(nbuckets + 256) / 256, 256, 0, st>>>(off_cur, nbuckets, cnt_tmp));
+        exclusive_scan(cnt_tmp, off_out, nbuckets + 1, s.block_sums, st);
+        uint32_t blocks = (uint32_t)(kNumSMs * round_blocks_per_sm);
+        {
+            uint64_t need = (ub_out / kMinSlots + 127) / 128 + 1;
+            if (need < blocks) blocks = (uint32_t)need;
+        }
+        const uint32_t rnt = blocks * 128;
+        RoundArgs ra;
+        ra.pts = pts_cur;
+        ra.sorted = sorted;
+        ra.off_in = off_cur;
+        ra.off_out = off_out;
+        ra.nbuckets = nbuckets;
+        ra.out = ((r & 1) ? s.pts_b : s.pts_a).as<G1Affine>(ub_out);
+        uint64_t p_max = (ub_out + rnt - 1) / rnt;
+        if (p_max < kMinSlots) p_max = kMinSlots;
+        ra.p_max = (uint32_t)p_max;
+        ra.pref = s.pref.as<Fp>(p_max * rnt);
+        ra.where = s.where.as<uint32_t>(p_max * rnt);
+        ra.dbg_in = ub;
+        ra.dbg_out = ub_out;
+        ra.dbg_tab = (uint64_t)(tab ? nwin : 1) * bases.n * batch;
+        if (r == 0) (++fb::g_launches, k_affine_round<true><<<blocks, 128, 0, st>>>(ra));
+        else (++fb::g_launches, k_affine_round<false><<<blocks, 128, 0, st>>>(ra));
+        pts_cur = ra.out;
+        off_cur = off_out;
+        ub = ub_out;
+    }
+
+    // accumulate: one wave of resident threads, equal chunks of the (remaining) entries
     prof_mark("msm.accumulate", st);
-    static int acc_blocks_per_sm = 0, acc_minb = 4;  // 4 blocks/SM (128 registers, 16 warps): measured 5% faster than 3
+    static int acc_blocks_per_sm = 0;
     if (!acc_blocks_per_sm) {
-        const char* e = getenv("FB_ACC_MINB");  // tuning knob
-        if (e && atoi(e) == 3) acc_minb = 3;
-        if (acc_minb == 4) FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate<4>, 128, 0));
-        else FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate<3>, 128, 0));
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&acc_blocks_per_sm, k_accumulate<4, false>, 128, 0));
         if (acc_blocks_per_sm < 1) acc_blocks_per_sm = 1;
     }
-    const uint64_t entries = (uint64_t)n * nwin;
     uint32_t acc_blocks = (uint32_t)(kNumSMs * acc_blocks_per_sm);
     {   // small inputs: no more threads than chunks of kMinChunk entries
-        uint64_t need = (entries / kMinChunk + 127) / 128 + 1;
+        uint64_t need = (ub / kMinChunk + 127) / 128 + 1;
         if (need < acc_blocks) acc_blocks = (uint32_t)need;
     }
     const uint32_t nt = acc_blocks * 128;
     G1Xyzz* partial = s.seg_t.as<G1Xyzz>((size_t)nbuckets + nt);
-    if (acc_minb == 4) (++fb::g_launches, k_accumulate<4><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
-    else (++fb::g_launches, k_accumulate<3><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
+    if (rounds > 0) (++fb::g_launches, k_accumulate<4, true><<<acc_blocks, 128, 0, st>>>(pts_cur, nullptr, off_cur, nbuckets, partial));
+    else (++fb::g_launches, k_accumulate<4, false><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
+    const uint32_t* offsets_final = off_cur;
     prof_mark("msm.combine", st);
     uint32_t* long_list = s.order.as<uint32_t>((size_t)nt + 2);
     FB_CUDA(cudaMemsetAsync(long_list, 0, sizeof(uint32_t), st));
-    (++fb::g_launches, k_combine<<<(nbuckets + 127) / 128, 128, 0, st>>>(partial, offsets, nbuckets, nt, buckets, long_list));
-    (++fb::g_launches, k_combine_long<<<2 * kNumSMs, kLongThreads, 0, st>>>(partial, offsets, nbuckets, nt, buckets, long_list));
+    (++fb::g_launches, k_combine<<<(nbuckets + 127) / 128, 128, 0, st>>>(partial, offsets_final, nbuckets, nt, buckets, long_list));
+    (++fb::g_launches, k_combine_long<<<2 * kNumSMs, kLongThreads, 0, st>>>(partial, offsets_final, nbuckets, nt, buckets, long_list));
 
     // bucket reduction
     prof_mark("msm.reduce", st);

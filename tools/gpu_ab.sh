@@ -1,6 +1,8 @@
 #!/bin/bash
-# A/B runs of the headline bench under env knobs, then one ncu --set full capture.
+# pytest under forced affine rounds, then A/B runs of the headline bench under env knobs, optional ncu --set full capture.
 mkdir -p gpurun_out
+FB_MSM_ROUNDS=3 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_rounds3.log 2>&1; echo "pytest(rounds=3) rc=$?"; tail -3 gpurun_out/pytest_rounds3.log
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 run() { # name, env...
   name=$1; shift
   env "$@" timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu > gpurun_out/ab_$name.json 2> gpurun_out/ab_$name.err || tail -5 gpurun_out/ab_$name.err
@@ -12,11 +14,12 @@ try:
 except Exception as e: print("$name failed", e)
 PY
 }
-run c20_occ3 FB_BENCH_WINDOW=20 FB_ACC_MINB=3
-run c20_occ4 FB_BENCH_WINDOW=20 FB_ACC_MINB=4
-run c17_occ4 FB_BENCH_WINDOW=17 FB_ACC_MINB=4
+for spec in $AB; do
+  name=${spec%%:*}; envs=${spec#*:}
+  run $name $(echo $envs | tr ',' ' ')
+done
 if [ -n "$NCU_KERNEL" ]; then
-FB_BENCH_WINDOW=20 timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/plain.log 2>&1 &&
-FB_BENCH_WINDOW=20 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$NCU_KERNEL" -s 4 -c 2 -f -o gpurun_out/prof_$NCU_TAG python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/ncu_full.log 2>&1
+env $NCU_ENV timeout 300 python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/plain.log 2>&1 &&
+env $NCU_ENV timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$NCU_KERNEL" -s ${NCU_SKIP:-4} -c 2 -f -o gpurun_out/prof_$NCU_TAG python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 fi
