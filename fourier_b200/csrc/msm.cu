@@ -8,9 +8,9 @@
 // falls into ONE set of 2^(c-1) buckets and no doubling ladder is needed at the end.
 //
 // Pipeline (all on one stream):
-//   1. k_digits<false>: scalar -> W signed c-bit digits; histogram of bucket sizes
+//   1. k_digits<0>: scalar -> W signed c-bit digits; histogram of bucket sizes
 //   2. exclusive scan of the histogram                       (bucket offsets)
-//   3. k_digits<true>: same digits again; scatter (point index | sign) into its
+//   3. k_digits<1|2>: same digits again; scatter (point index | sign), or the point, into its
 //      bucket's slice (a counting sort; order inside a bucket is irrelevant)
 //   4. k_accumulate: the sorted entries cut into equal chunks, one per resident thread,
 //      XYZZ += affine (8M+2S), points gathered by index from the resident table;
@@ -37,9 +37,24 @@ struct DigitArgs {
     uint32_t buckets_per_win;  // 2^(c-1) (index = |digit| - 1)
     uint32_t* counts;   // histogram (pass 0) / cursors (pass 1)
     uint32_t* sorted;
+    const G1Affine* pts;   // MODE 2: the resident points / table ...
+    G1Affine* sorted_pts;  // ... copied (sign applied) into bucket order
 };
 
-template <bool SCATTER>
+__device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p);
+__device__ __forceinline__ void st_affine(G1Affine* dst, const G1Affine& r) {
+    uint4* d = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+    for (int i = 0; i < 3; i++) d[i] = make_uint4(r.x.v[4 * i], r.x.v[4 * i + 1], r.x.v[4 * i + 2], r.x.v[4 * i + 3]);
+#pragma unroll
+    for (int i = 0; i < 3; i++) d[3 + i] = make_uint4(r.y.v[4 * i], r.y.v[4 * i + 1], r.y.v[4 * i + 2], r.y.v[4 * i + 3]);
+}
+
+// MODE 0: histogram of bucket sizes; 1: scatter (table index | sign) into bucket order;
+// 2: scatter the POINTS themselves (sign applied) into bucket order - the table is read
+// coalesced (thread = column) and the random side of the permutation is a write, so the
+// kernels that follow stream their inputs instead of gathering them.
+template <int MODE>
 __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.n) return;
@@ -80,12 +95,18 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
         uint32_t mag = neg ? (1u << a.c) - raw : raw;
         if (mag == 0) continue;
         uint32_t bucket = (a.tabulated ? row : row * a.nwin + (uint32_t)w) * a.buckets_per_win + mag - 1;
-        if (!SCATTER) {
+        if (MODE == 0) {
             atomicAdd(a.counts + bucket, 1u);
         } else {
             uint32_t slot = atomicAdd(a.counts + bucket, 1u);
             uint32_t idx = a.tabulated ? (row * a.nwin + (uint32_t)w) * a.stride + col : row * a.stride + col;
-            a.sorted[slot] = idx | ((neg ^ sneg) << 31);
+            if (MODE == 1) {
+                a.sorted[slot] = idx | ((neg ^ sneg) << 31);
+            } else {
+                G1Affine p = ldg_affine(a.pts + idx);
+                if (neg ^ sneg) p.y = fe_neg<FpParams>(p.y);
+                st_affine(a.sorted_pts + slot, p);
+            }
         }
     }
 }
@@ -169,33 +190,74 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
 //   pass 2  walks the slots backwards, peels off each pair's inverse and writes the sum.
 // After a few rounds the survivors (a few per bucket) go through the XYZZ kernel below.
 struct RoundArgs {
-    const G1Affine* pts;      // FIRST: the resident table (gathered through `sorted`); else the previous round's output
-    const uint32_t* sorted;   // FIRST only: table index | sign << 31
-    const uint32_t* off_in;   // [nbuckets + 1] bucket offsets of the input
+    const G1Affine* pts;      // GATHER: the resident table; else the previous round's output (bucket order)
     const uint32_t* off_out;  // [nbuckets + 1] bucket offsets of the output, off_out[b+1]-off_out[b] = ceil(count_in/2)
     uint32_t nbuckets;
     G1Affine* out;
-    Fp* pref;                 // [slot][thread] running products
-    uint32_t* where;          // [slot][thread] first input index of the slot | (has a second point) << 31
-    uint32_t p_max;           // slots per thread the scratch was sized for
-    uint64_t dbg_in, dbg_out, dbg_tab;  // element counts of the input / output / table arrays (bounds checks)
+    Fp* pref;                 // [step][thread] running products
+    const uint32_t* where;    // streamed: [slot] first input index | (has a second point) << 31
+    const uint2* where2;      // GATHER:   [slot] (table index | sign << 31) of both points, .y = kNone if single
+    uint32_t p_max;           // steps per thread the scratch was sized for
 };
 
 constexpr uint32_t kMinSlots = 16;
+constexpr uint32_t kNone = 0xffffffffu;
 
-template <bool FIRST>
-__device__ __forceinline__ G1Affine round_load(const RoundArgs& a, uint32_t e) {
-#ifdef FB_DEBUG_BOUNDS
-    if (e >= a.dbg_in) { printf("round_load: e=%u >= in=%llu (first=%d)\n", e, (unsigned long long)a.dbg_in, (int)FIRST); return G1Affine::inf(); }
-    if (FIRST && (a.sorted[e] & 0x7fffffffu) >= a.dbg_tab) { printf("round_load: ent=%u >= tab=%llu\n", a.sorted[e] & 0x7fffffffu, (unsigned long long)a.dbg_tab); return G1Affine::inf(); }
-#endif
-    if (FIRST) {
-        uint32_t ent = a.sorted[e];
-        G1Affine p = ldg_affine(a.pts + (ent & 0x7fffffffu));
-        if ((ent >> 31) && !p.is_inf()) p.y = fe_neg<FpParams>(p.y);
-        return p;
+// Slot map: for every output slot o (one thread per slot, binary search of its bucket) the
+// input(s) it adds.  GATHER (first round): the two table entries, so that the round kernel
+// needs no dependent index load and can prefetch one step ahead.
+template <bool GATHER>
+__global__ void __launch_bounds__(256) k_slot_map(const uint32_t* __restrict__ off_in, const uint32_t* __restrict__ off_out,
+                                                  uint32_t nbuckets, const uint32_t* __restrict__ sorted,
+                                                  uint32_t* __restrict__ where, uint2* __restrict__ where2) {
+    const uint32_t O = off_out[nbuckets];
+    for (uint32_t o = blockIdx.x * blockDim.x + threadIdx.x; o < O; o += gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = nbuckets;  // off_out[lo] <= o < off_out[hi]
+        while (hi - lo > 1) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (off_out[mid] <= o) lo = mid;
+            else hi = mid;
+        }
+        const uint32_t e = off_in[lo] + 2 * (o - off_out[lo]);
+        const bool has2 = e + 1 < off_in[lo + 1];
+        if (GATHER) where2[o] = make_uint2(sorted[e], has2 ? sorted[e + 1] : kNone);
+        else where[o] = e | (has2 ? 0x80000000u : 0u);
     }
-    return ldg_affine(a.pts + e);
+}
+
+template <bool GATHER>
+__device__ __forceinline__ uint2 slot_desc(const RoundArgs& a, uint32_t o) {
+    if (GATHER) return a.where2[o];
+    const uint32_t w = a.where[o], e = w & 0x7fffffffu;
+    return make_uint2(e, (w >> 31) ? e + 1 : kNone);
+}
+
+__device__ __forceinline__ void prefetch_point(const G1Affine* p) {
+    const char* c = reinterpret_cast<const char*>(p);
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 95));
+}
+__device__ __forceinline__ void prefetch_slot(const RoundArgs& a, uint2 d) {
+    prefetch_point(a.pts + (d.x & 0x7fffffffu));
+    if (d.y != kNone) prefetch_point(a.pts + (d.y & 0x7fffffffu));
+}
+
+// point i (bit 31 = negate) of the input
+__device__ __forceinline__ G1Affine load_point(const G1Affine* pts, uint32_t i) {
+    G1Affine p = ldg_affine(pts + (i & 0x7fffffffu));
+    if (i >> 31) p.y = fe_neg<FpParams>(p.y);
+    return p;
+}
+
+__device__ __forceinline__ Fp ldg_fp(const Fp* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    Fp r;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        uint4 t = __ldg(q + i);
+        r.v[4 * i] = t.x; r.v[4 * i + 1] = t.y; r.v[4 * i + 2] = t.z; r.v[4 * i + 3] = t.w;
+    }
+    return r;
 }
 
 // kind of a slot: 0 result = p1, 1 result = p2, 2 generic sum, 3 doubling, 4 identity
@@ -214,6 +276,23 @@ __device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2,
         return 3;
     }
     return 4;
+}
+
+// denominator of a slot from the x coordinates alone; the y coordinates are fetched only
+// when a special case is possible (x == 0 may be the identity (0,0); equal x is a doubling
+// or a cancellation)
+__device__ __forceinline__ Fp slot_den(const G1Affine* pts, uint2 d) {
+    using F = FpParams;
+    if (d.y == kNone) return Fp::one();
+    Fp x1 = ldg_fp(&pts[d.x & 0x7fffffffu].x), x2 = ldg_fp(&pts[d.y & 0x7fffffffu].x);
+    Fp dx = fe_sub<F>(x2, x1);
+    if (x1.is_zero() || x2.is_zero() || dx.is_zero()) {
+        G1Affine p1 = load_point(pts, d.x), p2 = load_point(pts, d.y);
+        Fp den;
+        (void)pair_kind(p1, p2, true, den);
+        return den;
+    }
+    return dx;
 }
 
 __device__ __forceinline__ Fp shfl_fp(const Fp& v, int src) {
@@ -246,82 +325,59 @@ __device__ __forceinline__ Fp warp_batch_inverse(const Fp& t) {
     return r;
 }
 
-template <bool FIRST>
+// A warp owns 32*P consecutive output slots; at step j lane l works on slot
+// base + 32*j + l, so the slot map, the points (2 x 96 B per lane, neighbouring lanes
+// neighbouring pairs) and the results are read and written as contiguous runs.
+template <bool GATHER>
 __global__ void __launch_bounds__(128, 4) k_affine_round(RoundArgs a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31;
     const uint32_t O = a.off_out[a.nbuckets];
     uint32_t P = (O + nt - 1) / nt;
     if (P < kMinSlots) P = kMinSlots;
     if (P > a.p_max) P = a.p_max;  // cannot happen: p_max comes from an upper bound on O
-    const uint64_t o0 = (uint64_t)t * P;
-    // NB: written as min(O - o0, P) ptxas 12.9 (sm_100a) fuses the subtraction and the min into
-    // VIADDMNMX.U32 with the operand's negation dropped (observed on B200: cnt == P for the last
-    // thread); the empty asm keeps the two apart.
-    uint32_t rem = o0 >= O ? 0u : O - (uint32_t)o0;
-    asm volatile("" : "+r"(rem));
-    const uint32_t cnt = rem < P ? rem : P;
-    if (__ballot_sync(0xffffffffu, cnt != 0) == 0) return;  // whole warp idle
-#ifdef FB_DEBUG_BOUNDS
-    if (t == 0) printf("k_affine_round first=%d O=%u nt=%u P=%u p_max=%u in=%llu out=%llu\n", (int)FIRST, O, nt, P, a.p_max, (unsigned long long)a.dbg_in, (unsigned long long)a.dbg_out);
-    if (O > a.dbg_out) { if (t == 0) printf("O exceeds out capacity\n"); return; }
-    if (t == 0 && a.nbuckets <= 4096) {
-        printf("  off_in=%p off_out=%p in[0..4]=%u %u %u %u %u out[0..4]=%u %u %u %u %u in[nb]=%u\n", a.off_in, a.off_out, a.off_in[0], a.off_in[1], a.off_in[2], a.off_in[3], a.off_in[4],
-               a.off_out[0], a.off_out[1], a.off_out[2], a.off_out[3], a.off_out[4], a.off_in[a.nbuckets]);
-        for (uint32_t b = 0; b < a.nbuckets; b++) {
-            uint32_t ci = a.off_in[b + 1] - a.off_in[b], co = a.off_out[b + 1] - a.off_out[b];
-            if (co != (ci + 1) / 2) { printf("  bucket %u: in %u..%u out %u..%u\n", b, a.off_in[b], a.off_in[b + 1], a.off_out[b], a.off_out[b + 1]); break; }
-        }
-    }
-#endif
+    const uint64_t base64 = (uint64_t)(t >> 5) * 32u * P;  // first slot of this warp
+    if (base64 >= O) return;                                // whole warp idle
+    const uint32_t base = (uint32_t)base64;
+    // steps of this lane: slots base + 32*j + lane < end = min(O, base + 32*P).
+    // NB: written as min(O - base, 32*P), ptxas 12.9 (sm_100a) fuses the subtraction and the min into
+    // VIADDMNMX.U32 with the negation of `base` dropped (seen on B200 as out-of-range slots); the
+    // add-then-min form below is what that instruction really computes.
+    uint64_t end64 = base64 + 32ull * P;
+    const uint32_t end = end64 < O ? (uint32_t)end64 : O;
+    const uint32_t avail = end - base;  // >= 1
+    const uint32_t cnt = avail > lane ? (avail - lane + 31u) / 32u : 0u;
 
-    // ---- pass 1
+    // ---- pass 1: running product of the denominators
     Fp run = Fp::one();
-    if (cnt) {
-        uint32_t o = (uint32_t)o0;
-        uint32_t lo = 0, hi = a.nbuckets;  // off_out[lo] <= o < off_out[hi]
-        while (hi - lo > 1) {
-            uint32_t mid = (lo + hi) >> 1;
-            if (a.off_out[mid] <= o) lo = mid;
-            else hi = mid;
+    uint2 dn = make_uint2(0u, kNone);  // descriptor of the next step, fetched (and its points prefetched) one step ahead
+    if (cnt) dn = slot_desc<GATHER>(a, base + lane);
+    for (uint32_t j = 0; j < cnt; j++) {
+        const uint2 d = dn;
+        if (j + 1 < cnt) {
+            dn = slot_desc<GATHER>(a, base + 32u * (j + 1) + lane);
+            if (GATHER) prefetch_slot(a, dn);
         }
-        uint32_t b = lo;
-        uint32_t ob = a.off_out[b], ob_next = a.off_out[b + 1];
-        uint32_t ib = a.off_in[b], ib_end = a.off_in[b + 1];
-        for (uint32_t j = 0; j < cnt; j++, o++) {
-            if (o == ob_next) {
-                do {
-                    b++;
-                    ob_next = a.off_out[b + 1];
-                } while (ob_next <= o);
-                ob = a.off_out[b];
-                ib = a.off_in[b];
-                ib_end = a.off_in[b + 1];
-            }
-            const uint32_t e = ib + 2 * (o - ob);
-            const bool has2 = e + 1 < ib_end;
-#ifdef FB_DEBUG_BOUNDS
-            if (e >= a.dbg_in) printf("pass1 t=%u o0=%u cnt=%u j=%u o=%u O=%u b=%u ob=%u ob_next=%u ib=%u ib_end=%u\n", t, (uint32_t)o0, cnt, j, o, O, b, ob, ob_next, ib, ib_end);
-#endif
-            G1Affine p1 = round_load<FIRST>(a, e);
-            G1Affine p2 = has2 ? round_load<FIRST>(a, e + 1) : G1Affine::inf();
-            Fp den;
-            (void)pair_kind(p1, p2, has2, den);
-            run = fe_mul<F>(run, den);
-            a.pref[(size_t)j * nt + t] = run;
-            a.where[(size_t)j * nt + t] = e | (has2 ? 0x80000000u : 0u);
-        }
+        Fp den = slot_den(a.pts, d);
+        run = fe_mul<F>(run, den);
+        a.pref[(size_t)j * nt + t] = run;
     }
     // ---- one inversion per warp
     Fp inv = warp_batch_inverse(run);
-    // ---- pass 2
+    // ---- pass 2: peel the inverses off backwards, add
+    if (cnt) dn = slot_desc<GATHER>(a, base + 32u * (cnt - 1) + lane);
     for (uint32_t j = cnt; j-- > 0;) {
-        const uint32_t w = a.where[(size_t)j * nt + t];
-        const uint32_t e = w & 0x7fffffffu;
-        const bool has2 = (w >> 31) != 0;
-        G1Affine p1 = round_load<FIRST>(a, e);
-        G1Affine p2 = has2 ? round_load<FIRST>(a, e + 1) : G1Affine::inf();
+        const uint32_t o = base + 32u * j + lane;
+        const uint2 d = dn;
+        if (j) {
+            dn = slot_desc<GATHER>(a, o - 32u);
+            if (GATHER) prefetch_slot(a, dn);
+        }
+        const bool has2 = d.y != kNone;
+        G1Affine p1 = load_point(a.pts, d.x);
+        G1Affine p2 = has2 ? load_point(a.pts, d.y) : G1Affine::inf();
         Fp den;
         const int kind = pair_kind(p1, p2, has2, den);
         Fp dinv = inv;
@@ -344,11 +400,7 @@ __global__ void __launch_bounds__(128, 4) k_affine_round(RoundArgs a) {
             r.x = x3;
             r.y = y3;
         }
-        uint4* dst = reinterpret_cast<uint4*>(a.out + ((uint32_t)o0 + j));
-#pragma unroll
-        for (int i = 0; i < 3; i++) dst[i] = make_uint4(r.x.v[4 * i], r.x.v[4 * i + 1], r.x.v[4 * i + 2], r.x.v[4 * i + 3]);
-#pragma unroll
-        for (int i = 0; i < 3; i++) dst[3 + i] = make_uint4(r.y.v[4 * i], r.y.v[4 * i + 1], r.y.v[4 * i + 2], r.y.v[4 * i + 3]);
+        st_affine(a.out + o, r);
     }
 }
 
@@ -698,8 +750,23 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     uint32_t* counts = s.counts.as<uint32_t>(nbuckets + 1);
     uint32_t* offsets = s.offsets.as<uint32_t>(nbuckets + 1);  // offsets[nbuckets] = number of entries
     uint32_t* cursor = s.cursor.as<uint32_t>(nbuckets + 1);
-    uint32_t* sorted = s.sorted.as<uint32_t>((size_t)n * nwin);
     G1Xyzz* buckets = s.buckets.as<G1Xyzz>(nbuckets);
+
+    // number of batched-affine rounds (0: gather + XYZZ only)
+    const uint64_t entries = (uint64_t)n * nwin;
+    static int rounds_env = -2, round_blocks_per_sm = 0;
+    if (rounds_env == -2) {
+        const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
+        rounds_env = e ? atoi(e) : -1;
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_affine_round<true>, 128, 0));
+        if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
+    }
+    // Measured on B200 (profiles/r1_v3_*): the first round gathers every point twice (6.6 GB of
+    // random 96-byte reads at ~2 TB/s) and ends up no faster than the XYZZ kernel, the later,
+    // streamed rounds run at ~78% of the multiplier peak.  Off by default until the gather is fixed.
+    int rounds = rounds_env >= 0 ? rounds_env : 0;
+    if (rounds > 8) rounds = 8;
+    uint32_t* sorted = s.sorted.as<uint32_t>(entries);
 
     prof_mark("msm.digits_count", st);
     FB_CUDA(cudaMemsetAsync(counts, 0, (nbuckets + 1) * sizeof(uint32_t), st));
@@ -715,35 +782,22 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     a.buckets_per_win = bpw;
     a.counts = counts;
     a.sorted = sorted;
+    a.pts = bases.pts;
+    a.sorted_pts = nullptr;  // MODE 2 (scatter the points, not their indices) measured slower: 1.5 ms of random 96-B writes
     DigitArgs a2 = a;
     const unsigned gb = (unsigned)((n + 255) / 256);
-    (++fb::g_launches, k_digits<false><<<gb, 256, 0, st>>>(a));
+    (++fb::g_launches, k_digits<0><<<gb, 256, 0, st>>>(a));
     prof_mark("msm.scan", st);
     exclusive_scan(counts, offsets, nbuckets + 1, s.block_sums, st);
     FB_CUDA(cudaMemcpyAsync(cursor, offsets, nbuckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     a2.counts = cursor;
     prof_mark("msm.scatter", st);
-    (++fb::g_launches, k_digits<true><<<gb, 256, 0, st>>>(a2));
+    (++fb::g_launches, k_digits<1><<<gb, 256, 0, st>>>(a2));
 
     // batched-affine halving rounds, then XYZZ accumulation of the survivors
-    const uint64_t entries = (uint64_t)n * nwin;
-    static int rounds_env = -2, round_blocks_per_sm = 0;
-    if (rounds_env == -2) {
-        const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
-        rounds_env = e ? atoi(e) : -1;
-        int b0 = 0, b1 = 0;
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_affine_round<true>, 128, 0));
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_affine_round<false>, 128, 0));
-        round_blocks_per_sm = b0 < b1 ? b0 : b1;
-        if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
-    }
-    int rounds = 0;
-    if (rounds_env >= 0) rounds = rounds_env;
-    else
-        while (rounds < 8 && (entries >> rounds) >= 1500000 && ((entries / nbuckets) >> rounds) >= 2) rounds++;
     const uint32_t* off_cur = offsets;
-    const G1Affine* pts_cur = bases.pts;
-    uint64_t ub = entries;  // upper bound on the number of live points
+    const G1Affine* pts_cur = bases.pts;   // round 0 gathers from the table through `sorted`
+    uint64_t ub = entries;                 // upper bound on the number of live points
     if (rounds > 0) prof_mark("msm.affine_rounds", st);
     for (int r = 0; r < rounds; r++) {
         const uint64_t ub_out = (ub + nbuckets) / 2 + 1;
@@ -759,8 +813,6 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         const uint32_t rnt = blocks * 128;
         RoundArgs ra;
         ra.pts = pts_cur;
-        ra.sorted = sorted;
-        ra.off_in = off_cur;
         ra.off_out = off_out;
         ra.nbuckets = nbuckets;
         ra.out = ((r & 1) ? s.pts_b : s.pts_a).as<G1Affine>(ub_out);
@@ -768,12 +820,18 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         if (p_max < kMinSlots) p_max = kMinSlots;
         ra.p_max = (uint32_t)p_max;
         ra.pref = s.pref.as<Fp>(p_max * rnt);
-        ra.where = s.where.as<uint32_t>(p_max * rnt);
-        ra.dbg_in = ub;
-        ra.dbg_out = ub_out;
-        ra.dbg_tab = (uint64_t)(tab ? nwin : 1) * bases.n * batch;
-        if (r == 0) (++fb::g_launches, k_affine_round<true><<<blocks, 128, 0, st>>>(ra));
-        else (++fb::g_launches, k_affine_round<false><<<blocks, 128, 0, st>>>(ra));
+        uint32_t* wbuf = s.where.as<uint32_t>(2 * ub_out);
+        ra.where = wbuf;
+        ra.where2 = reinterpret_cast<const uint2*>(wbuf);
+        uint64_t mb = (ub_out + 255) / 256;
+        if (mb > 4u * kNumSMs * 8u) mb = 4u * kNumSMs * 8u;
+        if (r == 0) {
+            (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
+            (++fb::g_launches, k_affine_round<true><<<blocks, 128, 0, st>>>(ra));
+        } else {
+            (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
+            (++fb::g_launches, k_affine_round<false><<<blocks, 128, 0, st>>>(ra));
+        }
         pts_cur = ra.out;
         off_cur = off_out;
         ub = ub_out;
