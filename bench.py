@@ -46,64 +46,7 @@ MSM_MAD_PER_POINT = {12: 66000, 20: 48000, 24: 39000}
 NTT_BYTES_PER_ELEM = 64
 
 
-def load_peaks():
-    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(p):
-        d = json.load(open(p))
-        return {"hbm_gbs": d.get("hbm_gbs", 6650.0), "source": "measured (MEASURED_PEAKS.json)"}
-    return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
-
-
-def load_int_peak():
-    """wide-MAD/s peak of the integer pipe, measured by tools/microbench (profiles/)."""
-    p = os.path.join(ROOT, "profiles", "int_peak.json")
-    if os.path.exists(p):
-        d = json.load(open(p))
-        return d["wide_mad_per_s"], "measured (profiles/int_peak.json: IMAD.WIDE.U32.X carry chains)"
-    return 148 * 32 * 1.965e9, "nominal 148 SM x 32 IMAD.WIDE/clk x 1.965 GHz"
-
-
-class ClockSampler:
-    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, index: int):
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.QUERY,
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
-                                      stderr=subprocess.DEVNULL)
-        except Exception:
-            self.p = None
-
-    def stop(self):
-        if self.p is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.p.terminate()
-        try:
-            self.p.wait(timeout=5)
-        except Exception:
-            self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
-        sm, mx, reasons = [], [], set()
-        for line in self.f.read().splitlines():
-            c = [x.strip() for x in line.split(",")]
-            if len(c) < 9:
-                continue
-            try:
-                sm.append(float(c[1]))
-                mx.append(float(c[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        os.unlink(self.f.name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+from fourier_b200.benchutil import ClockSampler, load_int_peak, load_peaks  # noqa: E402
 
 
 def reference_arm(args):
@@ -339,7 +282,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="kzg", choices=["kzg", "ntt", "msm", "bipoly"],
+                    help="kzg = the headline commit+open at 2^20 (default); the others are BASELINE configs 3-5")
+    ap.add_argument("--check", action="store_true", help="(msm, bipoly) also check the result against the oracle's known-dlog identity")
     args = ap.parse_args()
+    if args.workload != "kzg":
+        if args.impl == "reference":
+            raise SystemExit("--impl reference is defined for the headline workload only")
+        import bench_workloads
+        bench_workloads.RUN[args.workload](args)
+        return
     if args.impl == "reference":
         reference_arm(args)
     else:

@@ -1,0 +1,399 @@
+"""The other BASELINE.json workloads, behind `bench.py --workload {ntt,msm,bipoly}`:
+
+  ntt     config 3: Fr NTT / iNTT sweep 2^16 .. 2^24, single transform resident in HBM
+          (N GPUs = N independent replicas: a single NTT has no exchange step on this path)
+  msm     config 4: one G1 MSM of 2^24 points / random scalars, sharded by point ranges
+  bipoly  config 5: commit + open of 2^10 rows x 2^12 coefficients, rows sharded over the GPUs,
+          master_commit + master_open on rank 0
+
+Same JSON-line contract as bench.py (metric / value / e2e / roofline / clocks ...).
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+from fourier_b200.benchutil import ClockSampler, load_int_peak, load_peaks
+
+R = 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001
+SECRET_X, SECRET_Y = bytes([1] * 32), bytes([2] * 32)
+DTYPE = "u32 limbs (Fr 255-bit, Fp 381-bit Montgomery, exact integer)"
+
+
+def _env():
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    return torch, dist, rank, world, local, dev, stream
+
+
+def _barrier(torch, dist, world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(torch, dist, world, dev, vals):
+    if world == 1:
+        return vals
+    t = torch.tensor(vals, device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t]
+
+
+def _dev_fr(torch, be, dev, be_bytes_np):
+    """host (n,32) big-endian uint8 -> device Montgomery Fr tensor (n*32 bytes)"""
+    n = be_bytes_np.shape[0]
+    d_be = torch.from_numpy(be_bytes_np.reshape(-1)).to(dev)
+    d = torch.empty(n * 32, dtype=torch.uint8, device=dev)
+    be.dev_fr_from_be(d_be, d, n)
+    return d
+
+
+# ------------------------------------------------------------------ config 3: NTT sweep
+def run_ntt(args):
+    torch, dist, rank, world, local, dev, stream = _env()
+    from fourier_b200 import PianoBackend, synth
+    be = PianoBackend(24, 0, device=local)
+    be.set_stream(stream.cuda_stream)
+    peaks = load_peaks()
+    int_peak, int_src = load_int_peak()
+    sweep = {}
+    clocks = ClockSampler(local)
+    total_launches0 = be.launch_count()
+    ms_headline = None
+    for lg in (16, 18, 20, 22, 24):
+        n = 1 << lg
+        # enough distinct buffers that consecutive transforms never find their input in L2 (126 MB)
+        nbuf = max(1, min(64, (256 << 20) // (n * 32)))
+        host = synth.fr_bytes(40 + lg, n)
+        bufs = [_dev_fr(torch, be, dev, host) for _ in range(nbuf)]
+        out = torch.empty(n * 32, dtype=torch.uint8, device=dev)
+        res = {}
+        for inverse in (False, True):
+            for k in range(max(args.warmup, 3)):
+                be.dev_ntt(bufs[k % nbuf], out, n, inverse)
+            _barrier(torch, dist, world)
+            reps = max(args.steps, 10)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for k in range(reps):
+                be.dev_ntt(bufs[k % nbuf], out, n, inverse)
+            e1.record(stream)
+            _barrier(torch, dist, world)
+            ms = _max_over_ranks(torch, dist, world, dev, [e0.elapsed_time(e1) / reps])[0]
+            res["inverse" if inverse else "forward"] = ms
+        # round trip is the identity (size-independent parity property)
+        tmp = torch.empty_like(out)
+        be.dev_ntt(bufs[0], out, n, False)
+        be.dev_ntt(out, tmp, n, True)
+        torch.cuda.synchronize()
+        ok = bool(torch.equal(tmp, bufs[0]))
+        mul_per_elem = lg / 2 + (2 if lg > 10 else 0) + (2 if lg > 20 else 0)  # butterflies + inter-pass twiddles
+        sweep["2^%d" % lg] = {
+            "fwd_ms": res["forward"], "inv_ms": res["inverse"],
+            "gelem_per_s": world * n / (res["forward"] * 1e-3) / 1e9,
+            "hbm_gbs": n * 64 / (res["forward"] * 1e-3) / 1e9, "hbm_frac": n * 64 / (res["forward"] * 1e-3) / 1e9 / peaks["hbm_gbs"],
+            "int_frac": n * mul_per_elem * 128 / (res["forward"] * 1e-3) / int_peak,
+            "roundtrip_identity": ok, "buffers": nbuf}
+        if lg == 24:
+            ms_headline = res["forward"]
+        del bufs, out, tmp
+    clk = clocks.stop()
+    if rank == 0:
+        n = 1 << 24
+        line = {
+            "metric": "fr_ntt_gelem_per_s_2^24", "value": world * n / (ms_headline * 1e-3) / 1e9, "unit": "Gelem/s",
+            "n_gpus": world, "steps": max(args.steps, 10), "warmup": max(args.warmup, 3), "ms_per_step": ms_headline,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+            "config": {"workload": "Fr NTT sweep 2^16..2^24, natural order in/out (BASELINE config 3)",
+                       "parallelism": "1 GPU" if world == 1 else "%d independent replicas (a single NTT does not shard on this path)" % world,
+                       "l2": "inputs rotate over >= 256 MB of distinct buffers (larger than L2)"},
+            "e2e": None, "gpu_launches": int(be.launch_count() - total_launches0), "clocks": clk,
+            "roofline": {"kernel": "k_ntt_pass (3 passes at 2^24)", "bound": "hbm", "achieved": n * 64 / (ms_headline * 1e-3) / 1e9,
+                         "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": n * 64 / (ms_headline * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                         "traffic": None, "peak_source": peaks["source"],
+                         "note": "algorithmic bytes = 64 B/element (one read + one write); the binding limit is the integer "
+                                 "pipe (log2(N)/2 + 2 per pass boundary Fr multiplies of 128 wide MADs per element): see sweep[*].int_frac "
+                                 "against " + int_src},
+            "sweep": sweep,
+        }
+        print(json.dumps(line), flush=True)
+    be.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------ config 4: one big MSM
+def run_msm(args):
+    torch, dist, rank, world, local, dev, stream = _env()
+    from fourier_b200 import PianoBackend, synth
+    lg = int(os.environ.get("FB_MSM_LOG", "24"))
+    n = 1 << lg
+    per = n // world
+    start = rank * per
+    be = PianoBackend(10, 0, device=local)
+    be.set_stream(stream.cuda_stream)
+    t0 = time.time()
+    bases = be.bases_from_scalars(synth.fr_bytes(21, per, start))  # P_k = s_k * G
+    bases.precompute(int(os.environ.get("FB_BENCH_WINDOW", "0")))
+    torch.cuda.synchronize()
+    setup_s = time.time() - t0
+    h_scalars = torch.from_numpy(synth.fr_bytes(22, per, start).reshape(-1)).pin_memory()
+    d_scalars = torch.empty(per * 32, dtype=torch.uint8, device=dev)
+    be.dev_fr_from_be(h_scalars.to(dev), d_scalars, per)
+    d_out = torch.zeros(96, dtype=torch.uint8, device=dev)
+    gathered = torch.zeros(world * 96, dtype=torch.uint8, device=dev)
+
+    def step_device():
+        be.dev_msm_partial(bases, d_scalars, per, d_out)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, d_out)
+
+    def result():
+        parts = bytes((gathered if world > 1 else d_out).cpu().numpy())
+        return be.g1_sum(parts, fmt=96)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    _barrier(torch, dist, world)
+    l0 = be.launch_count()
+    clocks = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(torch, dist, world)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    _barrier(torch, dist, world)
+    ms_dev = e0.elapsed_time(e1) / args.steps
+    launches = be.launch_count() - l0
+    clk = clocks.stop()
+    res = result()
+
+    # e2e: scalars from pinned host memory through the public call, result read back
+    def step_host():
+        part = be.msm_partial(bases, h_scalars)
+        if world == 1:
+            return be.g1_sum(part, fmt=96)
+        mine = torch.frombuffer(bytearray(part), dtype=torch.uint8).to(dev)
+        dist.all_gather_into_tensor(gathered, mine)
+        return be.g1_sum(bytes(gathered.cpu().numpy()), fmt=96)
+
+    step_host()
+    _barrier(torch, dist, world)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        hres = step_host()
+    _barrier(torch, dist, world)
+    ms_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
+    ms_dev, ms_e2e = _max_over_ranks(torch, dist, world, dev, [ms_dev, ms_e2e])
+    assert hres == res, "host-API and device-resident results differ"
+
+    be.profile(True)
+    be.profile_read()
+    step_device()
+    torch.cuda.synchronize()
+    prof = be.profile_read()
+    be.profile(False)
+    if rank == 0:
+        peaks = load_peaks()
+        int_peak, int_src = load_int_peak()
+        mad_pp = {24: 39000, 20: 48000}.get(lg, 48000)
+        dom = max((k for k in prof if k.startswith("msm.")), key=lambda k: prof[k][0])
+        dom_s = prof[dom][0] / max(prof[dom][1], 1) * 1e-3
+        line = {
+            "metric": "g1_msm_mpts_per_s_2^%d" % lg, "value": n / (ms_dev * 1e-3) / 1e6, "unit": "Mpts/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+            "config": {"workload": "one G1 MSM of 2^%d points P_k = s_k*G with random 255-bit scalars (BASELINE config 4)" % lg,
+                       "parallelism": "1 GPU" if world == 1 else "point ranges over %d GPUs + all-gather of 96-byte partial sums" % world,
+                       "l2": "inputs larger than L2 (window tables + scalars)", "setup_s": round(setup_s, 2)},
+            "e2e": {"value": n / (ms_e2e * 1e-3) / 1e6, "unit": "Mpts/s", "h2d_bytes_per_step": per * 32,
+                    "d2h_bytes_per_step": 96 + (world * 96 if world > 1 else 0)},
+            "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"kernel": dom, "bound": "hbm", "achieved": per * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
+                         "unit": "GB/s", "frac": per * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                         "peak_source": peaks["source"],
+                         "note": "algorithmic bytes = 128 B/point; the binding limit is the integer pipe, see roofline_int"},
+            "roofline_int": {"kernel": "whole MSM", "bound": "int (IMAD.WIDE)", "achieved": n * mad_pp / (ms_dev * 1e-3) / 1e12,
+                             "peak": world * int_peak / 1e12, "unit": "T wide-MAD/s", "frac": n * mad_pp / (ms_dev * 1e-3) / (world * int_peak),
+                             "peak_source": int_src, "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp},
+            "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
+            "result": {"msm": res.hex()},
+        }
+        if args.check:  # known discrete logs: sum k_i * s_i in the exponent, one scalar multiplication in the oracle
+            from oracle import bls12_381 as bls
+            acc = 0
+            for lo in range(0, n, 1 << 18):
+                ss = synth.fr_ints(21, 1 << 18, lo)
+                ks = synth.fr_ints(22, 1 << 18, lo)
+                acc = (acc + sum(a * b for a, b in zip(ss, ks))) % R
+            line["parity"] = {"known_dlog_match": bls.g1_compress(bls.g1_mul(bls.G1_GEN, acc)) == res}
+        print(json.dumps(line), flush=True)
+    bases.free()
+    be.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------ config 5: bivariate rows
+def run_bipoly(args):
+    torch, dist, rank, world, local, dev, stream = _env()
+    from fourier_b200 import PianoBackend, synth
+    n_scale = int(os.environ.get("FB_BIPOLY_SCALE", "22"))
+    m_scale = int(os.environ.get("FB_BIPOLY_MSCALE", "10"))
+    M, T = 1 << m_scale, 1 << (n_scale - m_scale)
+    rows = M // world
+    row0 = rank * rows
+    be = PianoBackend(n_scale, m_scale, device=local, window_bits=int(os.environ.get("FB_BENCH_WINDOW", "0")))
+    be.set_stream(stream.cuda_stream)
+    t0 = time.time()
+    be.setup(SECRET_X, SECRET_Y, row0, rows)  # this rank keeps rows [row0, row0 + rows) of U resident
+    setup_s = time.time() - t0
+    coeffs_np = synth.fr_bytes(51, rows * T, row0 * T)  # the local rows of the 2^m x 2^t matrix (Lagrange basis)
+    alpha_b = synth.fr_bytes(53, 1).tobytes()
+    beta_b = synth.fr_bytes(54, 1).tobytes()
+    h_coeffs = torch.from_numpy(coeffs_np.reshape(-1)).pin_memory()
+    d_coeffs = _dev_fr(torch, be, dev, coeffs_np)
+    d_alpha = _dev_fr(torch, be, dev, synth.fr_bytes(53, 1))
+    d_out = torch.zeros(rows * 128, dtype=torch.uint8, device=dev)  # per row: 48 commit | 32 y | 48 proof
+    d_c, d_y, d_p = d_out[:rows * 48], d_out[rows * 48:rows * 80], d_out[rows * 80:]
+    gathered = torch.zeros(world * rows * 128, dtype=torch.uint8, device=dev) if world > 1 else None
+
+    def step_device():
+        be.dev_commit_rows(row0, rows, d_coeffs, T, d_c)
+        be.dev_open_rows(row0, rows, d_coeffs, T, d_alpha, d_y, d_p)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, d_out)
+
+    def unpack(buf: bytes):
+        cs, ys, ps = [], [], []
+        for k in range(world):
+            blk = buf[k * rows * 128:(k + 1) * rows * 128]
+            cs += [blk[i * 48:(i + 1) * 48] for i in range(rows)]
+            ys += [blk[rows * 48 + i * 32:rows * 48 + (i + 1) * 32] for i in range(rows)]
+            ps += [blk[rows * 80 + i * 48:rows * 80 + (i + 1) * 48] for i in range(rows)]
+        return cs, ys, ps
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    _barrier(torch, dist, world)
+    l0 = be.launch_count()
+    clocks = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    _barrier(torch, dist, world)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    _barrier(torch, dist, world)
+    ms_dev = e0.elapsed_time(e1) / args.steps
+    launches = be.launch_count() - l0
+    clk = clocks.stop()
+    cs, ys, ps = unpack(bytes((gathered if world > 1 else d_out).cpu().numpy()))
+
+    # e2e: host coefficient rows through commit_rows / open_rows, gather, master step on rank 0
+    def step_host():
+        c = be.commit_rows(row0, rows, h_coeffs)
+        y, p = be.open_rows(row0, rows, h_coeffs, alpha_b)
+        blob = b"".join(c) + b"".join(y) + b"".join(p)
+        if world > 1:
+            mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
+            dist.all_gather_into_tensor(gathered, mine)
+            blob = bytes(gathered.cpu().numpy())
+        if rank != 0:
+            return None
+        hc, hy, hp = unpack(blob)
+        com = be.master_commit(hc)
+        z, (pi0, pi1) = be.master_open(hy, hp, beta_b)
+        return hc, hy, hp, com, z, pi0, pi1
+
+    step_host()
+    _barrier(torch, dist, world)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        hres = step_host()
+    _barrier(torch, dist, world)
+    ms_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
+    ms_dev, ms_e2e = _max_over_ranks(torch, dist, world, dev, [ms_dev, ms_e2e])
+
+    be.profile(True)
+    be.profile_read()
+    step_device()
+    torch.cuda.synchronize()
+    prof = be.profile_read()
+    be.profile(False)
+    if rank == 0:
+        assert (hres[0], hres[1], hres[2]) == (cs, ys, ps), "host-API and device-resident results differ"
+        peaks = load_peaks()
+        int_peak, int_src = load_int_peak()
+        pts = 2 * M * T  # points through the MSMs of one step (commit + open)
+        msm_ms = sum(v[0] for k, v in prof.items() if k.startswith("msm."))
+        dom = max((k for k in prof if k.startswith("msm.")), key=lambda k: prof[k][0])
+        dom_s = prof[dom][0] / max(prof[dom][1], 1) * 1e-3
+        line = {
+            "metric": "bipoly_commit_open_ms_2^%dx2^%d" % (m_scale, n_scale - m_scale), "value": ms_dev, "unit": "ms",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev,
+            "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+            "config": {"workload": "bivariate (piano bench) worker commit+open of 2^%d rows x 2^%d coefficients "
+                                   "(scale=%d, machines_scale=%d, BASELINE config 5)" % (m_scale, n_scale - m_scale, n_scale, m_scale),
+                       "parallelism": "1 GPU" if world == 1 else "rows sharded over %d GPUs (%d rows each), all-gather of "
+                                      "128 bytes per row, master step on rank 0" % (world, rows),
+                       "l2": "inputs larger than L2 (window tables of the local rows + coefficient matrix)",
+                       "srs_setup_s": round(setup_s, 2)},
+            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * rows * T * 32 + 32,
+                    "d2h_bytes_per_step": rows * 128 + (world * rows * 128 if world > 1 else 0) + 128,
+                    "includes": "master_commit + master_open on rank 0"},
+            "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"kernel": dom, "bound": "hbm", "achieved": rows * T * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
+                         "unit": "GB/s", "frac": rows * T * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                         "peak_source": peaks["source"],
+                         "note": "algorithmic bytes = 128 B/point; the binding limit is the integer pipe, see roofline_int"},
+            "roofline_int": {"kernel": "row MSMs (commit + open)", "bound": "int (IMAD.WIDE)",
+                             "achieved": (pts / world) * 66000 / (msm_ms * 1e-3) / 1e12 if msm_ms else None, "peak": int_peak / 1e12,
+                             "unit": "T wide-MAD/s", "frac": (pts / world) * 66000 / (msm_ms * 1e-3) / int_peak if msm_ms else None,
+                             "peak_source": int_src, "work": "66000 wide-MAD/point at the fixed accounting window for 2^12 rows (SURVEY 8d)"},
+            "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
+            "extra": {"msm_mpts_per_s": pts / (ms_dev * 1e-3) / 1e6},
+            "result": {"master_commit": hres[3].hex(), "z": hres[4].hex(), "pi0": hres[5].hex(), "pi1": hres[6].hex()},
+        }
+        if args.check:
+            # known-tau identities on a sample of rows + the master pairing equation in the oracle
+            from oracle import bls12_381 as bls
+            from oracle import piano as opiano
+            o = opiano.PianoOracle(n_scale, m_scale)
+            o.generate_trusted_setup(SECRET_X, SECRET_Y, with_points=False)
+            alpha = int.from_bytes(alpha_b, "big")
+            beta = int.from_bytes(beta_b, "big")
+            okc = oko = True
+            for i in (0, 1, M // 2 + 3, M - 1):
+                row = synth.fr_ints(51, T, i * T)
+                okc &= cs[i] == bls.g1_compress(o.worker_commit_known_tau(i, row))
+                oy, opi = o.worker_open_known_tau(i, row, alpha)
+                oko &= ys[i] == oy.to_bytes(32, "big") and ps[i] == bls.g1_compress(opi)
+            line["parity"] = {"rows_commit_known_tau": bool(okc), "rows_open_known_tau": bool(oko)}
+            try:
+                line["parity"]["master_verify"] = bool(o.master_verify(
+                    bls.g1_decompress(hres[3]), beta, alpha, int.from_bytes(hres[4], "big"),
+                    (bls.g1_decompress(hres[5]), bls.g1_decompress(hres[6]))))
+            except Exception as exc:  # the oracle's pairing needs the G2 side of the setup
+                line["parity"]["master_verify"] = "skipped: %s" % exc
+        print(json.dumps(line), flush=True)
+    be.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+RUN = {"ntt": run_ntt, "msm": run_msm, "bipoly": run_bipoly}

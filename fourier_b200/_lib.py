@@ -49,6 +49,9 @@ SYMBOLS = [
     ("fb_dev_fr_to_be", C.c_int, [_ctx, C.c_void_p, C.c_void_p, C.c_uint64]),
     ("fb_dev_ntt", C.c_int, [_ctx, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]),
     ("fb_dev_msm", C.c_int, [_ctx, _bases, C.c_void_p, C.c_uint64, C.c_void_p]),
+    ("fb_dev_msm_partial", C.c_int, [_ctx, _bases, C.c_void_p, C.c_uint64, C.c_void_p]),
+    ("fb_dev_commit_rows", C.c_int, [_ctx, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]),
+    ("fb_dev_open_rows", C.c_int, [_ctx, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fb_dev_worker_commit", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]),
     ("fb_dev_worker_open", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     ("fb_ctx_set_col_shard", C.c_int, [_ctx, C.c_uint64, C.c_uint64]),

@@ -391,5 +391,17 @@ int fb_dev_msm(fb_ctx* c, const fb_bases* b, const void* d_scalars, uint64_t cou
         return FB_OK;
     });
 }
+int fb_dev_msm_partial(fb_ctx* c, const fb_bases* b, const void* d_scalars, uint64_t count, void* d_out96) {
+    return ctx_call(c, [&]() -> int {
+        if (!b || count > b->b.n) return ctx_fail(c, FB_ERR_ARG, "scalar count exceeds the base set");
+        G1Xyzz* d_r = c->small.as<G1Xyzz>(2);
+        msm_run(b->b, (const Fr*)d_scalars, count, 1, true, d_r, c->msm, c->stream);
+        G1Affine* aff = c->pt_b.as<G1Affine>(2);
+        prof_mark("out.affine_compress", c->stream);
+        g1_xyzz_to_affine_batch(d_r, aff, 1, c->stream);
+        g1_serialize_batch(aff, (uint8_t*)d_out96, 1, c->stream);
+        return FB_OK;
+    });
+}
 
 }  // extern "C"

@@ -102,9 +102,10 @@ struct TileTwiddles {
 };
 void ntt_build_tile_twiddles(TileTwiddles& t, cudaStream_t st);
 NttPlan ntt_make_plan(int log_n);
-// out may alias in; scratch must hold N elements when the plan has >= 2 passes
+// out may alias in; scratch must hold batch*N elements when the plan has >= 2 passes.
+// batch > 1: `batch` transforms of the same size, back to back in in/out/scratch.
 void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out, Fr* scratch, bool inverse,
-             cudaStream_t st);
+             cudaStream_t st, size_t batch = 1);
 
 // -------------------------------------------------------------- poly (poly.cu)
 // wire <-> device conversions and the Horner/quotient scan
@@ -114,7 +115,10 @@ void fr_fill_zero(Fr* d, size_t n, cudaStream_t st);
 // s_k = a_k + x*s_{k+1} (suffix Horner scan), s_n = 0.  Writes y = s_0 to d_y and,
 // when d_q != nullptr, q_k = s_{k+1} for k < n-1 and q_{n-1} = 0 (the zero-padded
 // quotient (p - y)/(X - x)).  d_x, d_y are single device Fr (Montgomery).
-void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st);
+// batch > 1: `batch` polynomials of n coefficients back to back (same x); d_y holds batch values,
+// d_q batch*n coefficients.
+void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st,
+                     size_t batch = 1);
 
 // ---------------------------------------------------------------- MSM (msm.cu)
 struct MsmBases {

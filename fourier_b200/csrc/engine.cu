@@ -103,15 +103,16 @@ void row_msm(fb_ctx* c, uint64_t i, const Fr* d_scalars, size_t len, G1Xyzz* d_o
     msm_run(row_bases(c, i), d_scalars + lo, hi - lo, 1, true, d_out, c->msm, c->stream);
 }
 
-// the field half of worker_open on device: d_coeffs (Montgomery, len) ->
-// y (d_y) and q_hat = NTT(q || 0) in c->fr_b.  Returns q_hat.
-Fr* open_scalars(fb_ctx* c, const NttTables& tab, const Fr* d_coeffs, size_t len, const Fr* d_alpha, Fr* d_y) {
-    Fr* d_poly = c->fr_b.as<Fr>(len);
-    Fr* d_tmp = c->fr_c.as<Fr>(len);
-    ntt_run(tab, c->tile_tw, d_coeffs, d_poly, d_tmp, true, c->stream);          // piano.rs:194
-    Fr* d_q = c->fr_a.as<Fr>(len);  // NB: callers keep d_coeffs elsewhere or accept the overwrite
-    horner_quotient(d_poly, len, d_alpha, d_y, d_q, c->scan, c->stream);           // :202-225
-    ntt_run(tab, c->tile_tw, d_q, d_poly, d_tmp, false, c->stream);               // :233
+// the field half of worker_open on device for `batch` rows at once: d_coeffs (Montgomery,
+// batch x len) -> y (d_y[batch]) and q_hat = NTT(q || 0) per row in c->fr_b.  Returns q_hat.
+Fr* open_scalars(fb_ctx* c, const NttTables& tab, const Fr* d_coeffs, size_t len, const Fr* d_alpha, Fr* d_y,
+                 size_t batch = 1) {
+    Fr* d_poly = c->fr_b.as<Fr>(len * batch);
+    Fr* d_tmp = c->fr_c.as<Fr>(len * batch);
+    ntt_run(tab, c->tile_tw, d_coeffs, d_poly, d_tmp, true, c->stream, batch);          // piano.rs:194
+    Fr* d_q = c->fr_a.as<Fr>(len * batch);  // NB: callers keep d_coeffs elsewhere or accept the overwrite
+    horner_quotient(d_poly, len, d_alpha, d_y, d_q, c->scan, c->stream, batch);           // :202-225
+    ntt_run(tab, c->tile_tw, d_q, d_poly, d_tmp, false, c->stream, batch);               // :233
     return d_poly;
 }
 
@@ -381,9 +382,12 @@ int fb_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs
         Fr* d_ys = d_all + nrows * len;
         fr_from_be(d_b, d_all, nrows * len, c->d_err, c->stream);
         G1Xyzz* d_r = (G1Xyzz*)c->eng_b.get((nrows + 1) * sizeof(G1Xyzz));
-        for (uint64_t r = 0; r < nrows; r++) {
-            Fr* d_qhat = open_scalars(c, tab, d_all + r * len, len, d_alpha, d_ys + r);
-            msm_run(row_bases(c, row0 + r), d_qhat, len, 1, true, d_r + r, c->msm, c->stream);  // piano.rs:228-236
+        // rows are independent: one batched iNTT / scan / NTT / MSM over slabs of rows
+        const uint64_t slab = 4096;
+        for (uint64_t r = 0; r < nrows; r += slab) {
+            const uint64_t rc2 = nrows - r < slab ? nrows - r : slab;
+            Fr* d_qhat = open_scalars(c, tab, d_all + r * len, len, d_alpha, d_ys + r, rc2);
+            msm_run(row_bases(c, row0 + r), d_qhat, len, rc2, true, d_r + r, c->msm, c->stream);  // piano.rs:228-236
         }
         uint8_t* d_ob = c->out_bytes.as<uint8_t>(80 * nrows);
         ctx_points_out(c, d_r, nrows, d_ob + 32 * nrows);
@@ -489,6 +493,46 @@ static int dev_open(fb_ctx* c, uint64_t i, const Fr* d_coeffs, uint64_t len, con
     fr_to_be(d_y, d_out, 1, c->stream);
     points_out_fmt(c, d_r, d_out + 32, fmt);
     return FB_OK;
+}
+
+// batched rows, operands in HBM: d_coeffs = nrows x len Montgomery Fr
+int fb_dev_commit_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const void* d_coeffs, uint64_t len, void* d_out48s) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, row0, nrows);
+        if (rc) return rc;
+        if ((rc = need_full_cols(c))) return rc;
+        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
+        if (nrows == 0) return FB_OK;
+        G1Xyzz* d_r = (G1Xyzz*)c->eng_b.get((nrows + 1) * sizeof(G1Xyzz));
+        msm_run(row_bases(c, row0), (const Fr*)d_coeffs, len, nrows, true, d_r, c->msm, c->stream);
+        ctx_points_out(c, d_r, nrows, (uint8_t*)d_out48s);
+        return FB_OK;
+    });
+}
+
+// d_out_ys: nrows x 32 bytes (big-endian), d_out_proofs: nrows x 48 bytes
+int fb_dev_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const void* d_coeffs, uint64_t len, const void* d_alpha,
+                     void* d_out_ys, void* d_out_proofs) {
+    return ctx_call(c, [&]() -> int {
+        int rc = need_row(c, row0, nrows);
+        if (rc) return rc;
+        if ((rc = need_full_cols(c))) return rc;
+        int lg = ilog2_exact(len);
+        if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+        if (nrows == 0) return FB_OK;
+        const NttTables& tab = ctx_ntt_tables(c, lg);
+        Fr* d_ys = (Fr*)c->eng_a.get((nrows + 1) * sizeof(Fr));
+        G1Xyzz* d_r = (G1Xyzz*)c->eng_b.get((nrows + 1) * sizeof(G1Xyzz));
+        const uint64_t slab = 4096;
+        for (uint64_t r = 0; r < nrows; r += slab) {
+            const uint64_t rc2 = nrows - r < slab ? nrows - r : slab;
+            Fr* d_qhat = open_scalars(c, tab, (const Fr*)d_coeffs + r * len, len, (const Fr*)d_alpha, d_ys + r, rc2);
+            msm_run(row_bases(c, row0 + r), d_qhat, len, rc2, true, d_r + r, c->msm, c->stream);
+        }
+        fr_to_be(d_ys, (uint8_t*)d_out_ys, nrows, c->stream);
+        ctx_points_out(c, d_r, nrows, (uint8_t*)d_out_proofs);
+        return FB_OK;
+    });
 }
 
 int fb_ctx_set_col_shard(fb_ctx* c, uint64_t col0, uint64_t ncols) {

@@ -86,6 +86,7 @@ struct PassArgs {
     const Fr* tw_hi;
     const Fr* tile_tw;
     const Fr* n_inv;
+    unsigned long long batch_stride;  // elements between consecutive transforms of a batch (blockIdx.y)
 };
 
 __device__ __forceinline__ Fr lds_fr(const uint4* p0, const uint4* p1, uint32_t e) {
@@ -118,10 +119,12 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
     uint4* t1 = t0 + (R >> 1);
     const uint32_t tid = threadIdx.x, nt = blockDim.x;
     const unsigned long long c0 = (unsigned long long)blockIdx.x << a.log_b;
+    const Fr* in = a.in + (unsigned long long)blockIdx.y * a.batch_stride;
+    Fr* out = a.out + (unsigned long long)blockIdx.y * a.batch_stride;
 
     for (uint32_t e = tid; e < tile; e += nt) {
         uint32_t cb = e & (B - 1), r = e >> a.log_b;
-        const uint4* src = reinterpret_cast<const uint4*>(a.in + ((unsigned long long)r * a.C + c0 + cb));
+        const uint4* src = reinterpret_cast<const uint4*>(in + ((unsigned long long)r * a.C + c0 + cb));
         s0[e] = src[0];
         s1[e] = src[1];
     }
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
         }
         if (a.scale) val = fe_mul<FrParams>(val, ninv);
         unsigned long long o = (rest << (a.log_q + a.log_r)) | ((unsigned long long)k << a.log_q) | (c & qmask);
-        uint4* dst = reinterpret_cast<uint4*>(a.out + o);
+        uint4* dst = reinterpret_cast<uint4*>(out + o);
         dst[0] = make_uint4(val.v[0], val.v[1], val.v[2], val.v[3]);
         dst[1] = make_uint4(val.v[4], val.v[5], val.v[6], val.v[7]);
     }
@@ -245,7 +248,9 @@ void ntt_free_tables(NttTables& t) {
 }
 
 void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out, Fr* scratch, bool inverse,
-             cudaStream_t st) {
+             cudaStream_t st, size_t batch) {
+    if (batch == 0) return;
+    if (batch > 65535) throw CudaError{"ntt: batch too large"};
     static bool attr_set = false;
     if (!attr_set) {
         FB_CUDA(cudaFuncSetAttribute(k_ntt_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -286,7 +291,8 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         unsigned long long blocks = a.C >> a.log_b;
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
         prof_mark(names[j], st);
-        (++fb::g_launches, k_ntt_pass<<<(unsigned)blocks, threads, smem, st>>>(a));
+        a.batch_stride = 1ull << log_n;
+        (++fb::g_launches, k_ntt_pass<<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
         src = dst;
         log_q += a.log_r;
     }

@@ -73,10 +73,15 @@ __global__ void k_level_pows(const Fr* x, Fr* pows, int levels) {
     }
 }
 
+// All scan kernels take a batch of polynomials: row r (blockIdx.y, or the thread index in
+// k_horner_top) reads a + r*n and writes its outputs r*<row length> further on.
+
 // h[j] = sum_i a[j*L + i] * beta^i
 __global__ void k_horner_up(const Fr* __restrict__ a, size_t n, const Fr* beta_p, Fr* __restrict__ h, size_t nchunks) {
     size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= nchunks) return;
+    a += (size_t)blockIdx.y * n;
+    h += (size_t)blockIdx.y * nchunks;
     const Fr beta = *beta_p;
     size_t lo = j << kChunkLog;
     size_t hi = lo + kChunk < n ? lo + kChunk : n;
@@ -85,9 +90,12 @@ __global__ void k_horner_up(const Fr* __restrict__ a, size_t n, const Fr* beta_p
     h[j] = acc;
 }
 
-// sequential suffix scan of a short array: s[j] = a[j] + beta*s[j+1]
-__global__ void k_horner_top(const Fr* a, size_t n, const Fr* beta_p, Fr* s) {
-    if (threadIdx.x || blockIdx.x) return;
+// sequential suffix scan of a short array: s[j] = a[j] + beta*s[j+1]; one thread per row
+__global__ void k_horner_top(const Fr* a, size_t n, const Fr* beta_p, Fr* s, size_t batch) {
+    size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= batch) return;
+    a += r * n;
+    s += r * n;
     const Fr beta = *beta_p;
     Fr acc = Fr::zero();
     for (size_t k = n; k > 0; k--) {
@@ -103,6 +111,10 @@ __global__ void k_horner_down(const Fr* __restrict__ a, size_t n, const Fr* beta
                               size_t nchunks, Fr* __restrict__ s_out, int mode, Fr* y_out) {
     size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= nchunks) return;
+    a += (size_t)blockIdx.y * n;
+    s_out += (size_t)blockIdx.y * n;
+    if (up_s) up_s += (size_t)blockIdx.y * nchunks;
+    if (y_out) y_out += blockIdx.y;
     const Fr beta = *beta_p;
     size_t lo = j << kChunkLog;
     size_t hi = lo + kChunk < n ? lo + kChunk : n;
@@ -118,6 +130,12 @@ __global__ void k_horner_down(const Fr* __restrict__ a, size_t n, const Fr* beta
             *y_out = acc;
         }
     }
+}
+
+// y[r] = s[r*stride]
+__global__ void k_gather_first(const Fr* __restrict__ s, size_t stride, Fr* __restrict__ y, size_t batch) {
+    size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < batch) y[r] = s[r * stride];
 }
 
 }  // namespace
@@ -141,24 +159,29 @@ void fr_fill_zero(Fr* d, size_t n, cudaStream_t st) {
     FB_CUDA(cudaGetLastError());
 }
 
-void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st) {
+void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st,
+                     size_t batch) {
+    if (batch == 0) return;
+    if (batch > 65535) throw CudaError{"horner_quotient: batch too large"};
     if (n == 0) {
-        FB_CUDA(cudaMemsetAsync(d_y, 0, sizeof(Fr), st));
+        FB_CUDA(cudaMemsetAsync(d_y, 0, batch * sizeof(Fr), st));
         return;
     }
     prof_mark("poly.scan", st);
-    // level sizes
+    // level sizes (per row)
     std::vector<size_t> sz{n};
     while (sz.back() > (size_t)kChunk) sz.push_back((sz.back() + kChunk - 1) >> kChunkLog);
     const int levels = (int)sz.size() - 1;  // number of up-sweeps
     size_t total = 0;
     for (int l = 1; l <= levels; l++) total += sz[l];
-    // scratch: pows[levels+1] | h_1..h_levels | s_1..s_levels | s_top(for levels==0)
-    Fr* base = scratch.as<Fr>((size_t)(levels + 2) + 2 * total + kChunk + 8);
+    // scratch: pows[levels+2] | h_1..h_levels | s_1..s_levels | s_top (levels == 0), each batch rows deep
+    Fr* base = scratch.as<Fr>((size_t)(levels + 2) + batch * (2 * total + kChunk) + 8);
     Fr* pows = base;
     Fr* hbuf = base + levels + 2;
-    Fr* sbuf = hbuf + total;
-    Fr* stop = sbuf + total;
+    Fr* sbuf = hbuf + batch * total;
+    Fr* stop = sbuf + batch * total;
+    const unsigned by = (unsigned)batch;
+    const unsigned tb = (unsigned)((batch + 63) / 64);
     (++fb::g_launches, k_level_pows<<<1, 1, 0, st>>>(d_x, pows, levels));
     std::vector<const Fr*> arr(levels + 1);
     std::vector<Fr*> sarr(levels + 1, nullptr);
@@ -167,34 +190,34 @@ void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, D
         Fr* hp = hbuf;
         Fr* sp = sbuf;
         for (int l = 1; l <= levels; l++) {
-            (++fb::g_launches, k_horner_up<<<(unsigned)((sz[l] + 127) / 128), 128, 0, st>>>(arr[l - 1], sz[l - 1], pows + (l - 1), hp, sz[l]));
+            (++fb::g_launches, k_horner_up<<<dim3((unsigned)((sz[l] + 127) / 128), by), 128, 0, st>>>(arr[l - 1], sz[l - 1], pows + (l - 1), hp, sz[l]));
             arr[l] = hp;
             sarr[l] = sp;
-            hp += sz[l];
-            sp += sz[l];
+            hp += batch * sz[l];
+            sp += batch * sz[l];
         }
     }
     if (levels == 0) {
-        // short input: one thread does it all
+        // short input: one thread per row does it all
         if (d_q) {
-            (++fb::g_launches, k_horner_down<<<1, 1, 0, st>>>(d_a, n, pows, nullptr, 1, d_q, 1, d_y));
+            (++fb::g_launches, k_horner_down<<<dim3(1, by), 1, 0, st>>>(d_a, n, pows, nullptr, 1, d_q, 1, d_y));
         } else {
-            (++fb::g_launches, k_horner_top<<<1, 1, 0, st>>>(d_a, n, pows, stop));
-            FB_CUDA(cudaMemcpyAsync(d_y, stop, sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+            (++fb::g_launches, k_horner_top<<<tb, 64, 0, st>>>(d_a, n, pows, stop, batch));
+            (++fb::g_launches, k_gather_first<<<tb, 64, 0, st>>>(stop, n, d_y, batch));
         }
         FB_CUDA(cudaGetLastError());
         return;
     }
-    (++fb::g_launches, k_horner_top<<<1, 1, 0, st>>>(arr[levels], sz[levels], pows + levels, sarr[levels]));
+    (++fb::g_launches, k_horner_top<<<tb, 64, 0, st>>>(arr[levels], sz[levels], pows + levels, sarr[levels], batch));
     if (!d_q) {
-        FB_CUDA(cudaMemcpyAsync(d_y, sarr[levels], sizeof(Fr), cudaMemcpyDeviceToDevice, st));
+        (++fb::g_launches, k_gather_first<<<tb, 64, 0, st>>>(sarr[levels], sz[levels], d_y, batch));
         FB_CUDA(cudaGetLastError());
         return;
     }
     for (int l = levels - 1; l >= 1; l--)
-        (++fb::g_launches, k_horner_down<<<(unsigned)((sz[l + 1] + 127) / 128), 128, 0, st>>>(arr[l], sz[l], pows + l, sarr[l + 1], sz[l + 1],
+        (++fb::g_launches, k_horner_down<<<dim3((unsigned)((sz[l + 1] + 127) / 128), by), 128, 0, st>>>(arr[l], sz[l], pows + l, sarr[l + 1], sz[l + 1],
                                                                             sarr[l], 0, nullptr));
-    (++fb::g_launches, k_horner_down<<<(unsigned)((sz[1] + 127) / 128), 128, 0, st>>>(d_a, n, pows, sarr[1], sz[1], d_q, 1, d_y));
+    (++fb::g_launches, k_horner_down<<<dim3((unsigned)((sz[1] + 127) / 128), by), 128, 0, st>>>(d_a, n, pows, sarr[1], sz[1], d_q, 1, d_y));
     FB_CUDA(cudaGetLastError());
 }
 

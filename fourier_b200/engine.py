@@ -328,6 +328,16 @@ class PianoBackend:
     def dev_msm(self, bases: Bases, d_scalars, count: int, d_out48):
         self._chk(self._lib.fb_dev_msm(self._ctx, bases._h, _lib.addr(d_scalars), count, _lib.addr(d_out48)))
 
+    def dev_msm_partial(self, bases: Bases, d_scalars, count: int, d_out96):
+        self._chk(self._lib.fb_dev_msm_partial(self._ctx, bases._h, _lib.addr(d_scalars), count, _lib.addr(d_out96)))
+
+    def dev_commit_rows(self, row0: int, nrows: int, d_coeffs, length: int, d_out48s):
+        self._chk(self._lib.fb_dev_commit_rows(self._ctx, row0, nrows, _lib.addr(d_coeffs), length, _lib.addr(d_out48s)))
+
+    def dev_open_rows(self, row0: int, nrows: int, d_coeffs, length: int, d_alpha, d_out_ys, d_out_proofs):
+        self._chk(self._lib.fb_dev_open_rows(self._ctx, row0, nrows, _lib.addr(d_coeffs), length, _lib.addr(d_alpha),
+                                             _lib.addr(d_out_ys), _lib.addr(d_out_proofs)))
+
     def dev_worker_commit(self, i: int, d_coeffs, count: int, d_out48):
         self._chk(self._lib.fb_dev_worker_commit(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_out48)))
 

@@ -156,6 +156,15 @@ int fb_dev_worker_commit_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_f
 int fb_dev_worker_open_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
                                void* d_out128);
 
+/* uncompressed (96-byte) result, for the partial sums of an MSM sharded by point ranges */
+int fb_dev_msm_partial(fb_ctx* ctx, const fb_bases* b, const void* d_scalars_fr, uint64_t count, void* d_out96);
+/* batched rows (the bivariate row loop of src/bipoly.rs / benches/piano.rs:41-63), operands
+ * in HBM: d_coeffs_fr = nrows x len Montgomery Fr; outputs nrows x 48 / nrows x 32 bytes */
+int fb_dev_commit_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d_coeffs_fr, uint64_t len,
+                       void* d_out48s);
+int fb_dev_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d_coeffs_fr, uint64_t len,
+                     const void* d_alpha_fr, void* d_out_ys_be, void* d_out_proof48s);
+
 /* number of kernel launches issued by this library so far */
 uint64_t fb_launch_count(const fb_ctx* ctx);
 /* per-phase device timing (CUDA events on the launching stream); fb_prof_read

@@ -190,3 +190,32 @@ def test_c2_degree_2_20_known_tau(gpu):
     oy, opi = o.worker_open_known_tau(0, coeffs, alpha)
     assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
     b.close()
+
+
+def test_device_resident_rows_match_host_api(small):
+    """fb_dev_commit_rows / fb_dev_open_rows (operands in HBM, batched iNTT + scan + NTT + MSM
+    over all rows) return the bytes of the per-row host calls."""
+    import torch
+    b, o = small
+    rng = random.Random(12)
+    rows = [[rng.randrange(R) for _ in range(o.T)] for _ in range(o.M)]
+    alpha = rng.randrange(R)
+    flat = fr_list_to_bytes([x for row in rows for x in row])
+    dev = torch.device("cuda", 0)
+    d_be = torch.frombuffer(bytearray(flat), dtype=torch.uint8).to(dev)
+    d_fr = torch.empty_like(d_be)
+    b.dev_fr_from_be(d_be, d_fr, o.M * o.T)
+    d_a_be = torch.frombuffer(bytearray(alpha.to_bytes(32, "big")), dtype=torch.uint8).to(dev)
+    d_alpha = torch.empty_like(d_a_be)
+    b.dev_fr_from_be(d_a_be, d_alpha, 1)
+    d_c = torch.zeros(o.M * 48, dtype=torch.uint8, device=dev)
+    d_y = torch.zeros(o.M * 32, dtype=torch.uint8, device=dev)
+    d_p = torch.zeros(o.M * 48, dtype=torch.uint8, device=dev)
+    b.dev_commit_rows(0, o.M, d_fr, o.T, d_c)
+    b.dev_open_rows(0, o.M, d_fr, o.T, d_alpha, d_y, d_p)
+    b.sync()
+    cs, ys, ps = bytes(d_c.cpu().numpy()), bytes(d_y.cpu().numpy()), bytes(d_p.cpu().numpy())
+    for i in range(o.M):
+        assert cs[i * 48:(i + 1) * 48] == b.worker_commit(i, rows[i])
+        y, pi = b.worker_open(i, rows[i], alpha)
+        assert ys[i * 32:(i + 1) * 32] == y and ps[i * 48:(i + 1) * 48] == pi
