@@ -215,7 +215,7 @@ def own_arm(args):
         peaks = load_peaks()
         int_peak, int_src = load_int_peak()
         nw = lambda c: (255 + c - 1) // c
-        wbits = WINDOW if WINDOW else min(range(4, 23), key=lambda c: ncols * nw(c) * 10 + (1 << (c - 1)) * 28)  # msm_pick_window
+        wbits = WINDOW if WINDOW else min(range(4, 23), key=lambda c: ncols * nw(c) * 10 + (1 << (c - 1)) * 60)  # msm_pick_window
         table_windows = (255 + wbits - 1) // wbits
         acc_ms, acc_cnt = prof.get("msm.accumulate", (0.0, 1))
         acc_avg_s = acc_ms / max(acc_cnt, 1) * 1e-3
@@ -235,7 +235,7 @@ def own_arm(args):
                                    "bit-exact vs CPU oracle" % (SCALE, SCALE),
                        "parallelism": "1 GPU" if world == 1 else "MSM point ranges over %d GPUs + all-gather of 224-byte partials" % world,
                        "l2": "inputs larger than L2: window tables %.2f GB per GPU + 32 MiB coefficients" %
-                             (table_windows * ncols * 96 / 1e9), "window_bits": wbits, "srs_setup_s": round(setup_s, 2), "seed": [SEED_COEFFS, SEED_ALPHA]},
+                             (table_windows * ncols * 128 / 1e9), "window_bits": wbits, "srs_setup_s": round(setup_s, 2), "seed": [SEED_COEFFS, SEED_ALPHA]},
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * n * 32 + 32, "d2h_bytes_per_step": 48 + 32 + 48
                     if world == 1 else 96 + 32 + 96 + world * 224},
             "gpu_launches": int(launches),

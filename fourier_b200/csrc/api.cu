@@ -112,7 +112,7 @@ void fb_ctx_destroy(fb_ctx* c) {
     if (c->d_u) cudaFree(c->d_u);
     DevBuf* bufs[] = {&c->msm.counts, &c->msm.offsets, &c->msm.cursor, &c->msm.sorted, &c->msm.buckets, &c->msm.block_sums,
                       &c->msm.seg_a, &c->msm.seg_t, &c->msm.order, &c->msm.misc, &c->msm.pts_a, &c->msm.pts_b, &c->msm.pref,
-                      &c->msm.where, &c->in_bytes, &c->fr_a, &c->fr_b, &c->fr_c,
+                      &c->msm.where, &c->msm.stage, &c->msm.inv, &c->in_bytes, &c->fr_a, &c->fr_b, &c->fr_c,
                       &c->pt_a, &c->pt_b, &c->out_bytes, &c->scan, &c->small, &c->eng_a, &c->eng_b};
     for (DevBuf* b : bufs) b->release();
     if (c->d_err) cudaFree(c->d_err);
@@ -286,8 +286,8 @@ int fb_bases_precompute(fb_ctx* c, fb_bases* b, int window_bits) {
         int cc = window_bits > 0 ? window_bits : msm_pick_window(b->b.n, true);
         if (cc < 4 || cc > 24) return ctx_fail(c, FB_ERR_ARG, "window bits out of range");
         int nwin = msm_num_windows(cc);
-        G1Affine* tab;
-        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * b->b.n * sizeof(G1Affine)));
+        void* tab;
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * b->b.n * kTableStride));
         msm_build_table(b->raw, b->b.n, 1, cc, nwin, tab, c->pt_a, c->stream);
         FB_CUDA(cudaStreamSynchronize(c->stream));
         if (b->b.pts != b->raw) cudaFree(b->b.pts);

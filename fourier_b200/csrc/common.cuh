@@ -121,15 +121,20 @@ void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, D
                      size_t batch = 1);
 
 // ---------------------------------------------------------------- MSM (msm.cu)
+// Window-table entries are padded to one 128-byte line (x in the first 64-byte DRAM atom):
+// a gathered point is exactly one line, and the batched-affine rounds' first pass, which
+// needs x only, touches one atom.  Untabulated bases stay packed (96 bytes).
+constexpr uint32_t kTableStride = 128;
 struct MsmBases {
-    G1Affine* pts = nullptr;  // [rows][nwin][n] when tabulated (window w holds 2^(c*w) * P), else [rows][n]
+    void* pts = nullptr;      // [rows][nwin][n] x 128 B when tabulated (window w holds 2^(c*w) * P), else [rows][n] x 96 B
     size_t n = 0;             // row length
     int c = 0;                // window bits of the table (0: no table)
     int nwin = 0;
+    uint32_t stride() const { return c > 0 ? kTableStride : (uint32_t)sizeof(G1Affine); }
 };
 
 struct MsmScratch {
-    DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc, pts_a, pts_b, pref, where;
+    DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc, pts_a, pts_b, pref, where, stage, inv;
 };
 
 // d_out[b] (device XYZZ) = sum_k scalars[b*len + k] * bases_b[k] for b < batch, where
@@ -137,8 +142,8 @@ struct MsmScratch {
 // in Montgomery form (scalars_mont) or canonical little-endian limbs.
 void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
              MsmScratch& s, cudaStream_t st);
-// table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin
-void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, G1Affine* d_out, DevBuf& scratch,
+// table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin, kTableStride bytes per entry
+void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, void* d_out, DevBuf& scratch,
                      cudaStream_t st);
 int msm_pick_window(size_t n, bool tabulated);
 int msm_num_windows(int c);  // ceil(255 / c)

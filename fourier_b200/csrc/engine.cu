@@ -45,8 +45,8 @@ void srs_build_tables(fb_ctx* c) {
         int cc = c->window_pref > 0 ? c->window_pref : msm_pick_window(c->ncols, true);
         if (cc < 2 || cc > 24) throw CudaError{"window bits out of range (2..24)"};
         int nwin = msm_num_windows(cc);
-        G1Affine* tab;
-        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->ncols * c->nrows * sizeof(G1Affine)));
+        void* tab;
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->ncols * c->nrows * kTableStride));
         msm_build_table(c->d_u, c->ncols, c->nrows, cc, nwin, tab, c->pt_a, c->stream);
         c->u_bases.pts = tab;
         c->u_bases.c = cc;
@@ -55,8 +55,8 @@ void srs_build_tables(fb_ctx* c) {
     if (c->M >= 16) {
         int cc = msm_pick_window(c->M, true);
         int nwin = msm_num_windows(cc);
-        G1Affine* tab;
-        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->M * sizeof(G1Affine)));
+        void* tab;
+        FB_CUDA(cudaMalloc(&tab, (size_t)nwin * c->M * kTableStride));
         msm_build_table(c->d_g_tau_y, c->M, 1, cc, nwin, tab, c->pt_a, c->stream);
         c->y_bases.pts = tab;
         c->y_bases.c = cc;
@@ -79,7 +79,7 @@ int check_rows(fb_ctx* c, uint64_t& row0, uint64_t& nrows) {
 MsmBases row_bases(fb_ctx* c, uint64_t i) {
     MsmBases b = c->u_bases;
     size_t per_row = (size_t)(b.c > 0 ? b.nwin : 1) * c->ncols;
-    b.pts = c->u_bases.pts + (i - c->row0) * per_row;
+    b.pts = (char*)c->u_bases.pts + (i - c->row0) * per_row * b.stride();
     return b;
 }
 

@@ -37,8 +37,6 @@ struct DigitArgs {
     uint32_t buckets_per_win;  // 2^(c-1) (index = |digit| - 1)
     uint32_t* counts;   // histogram (pass 0) / cursors (pass 1)
     uint32_t* sorted;
-    const G1Affine* pts;   // MODE 2: the resident points / table ...
-    G1Affine* sorted_pts;  // ... copied (sign applied) into bucket order
 };
 
 __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p);
@@ -50,10 +48,9 @@ __device__ __forceinline__ void st_affine(G1Affine* dst, const G1Affine& r) {
     for (int i = 0; i < 3; i++) d[3 + i] = make_uint4(r.y.v[4 * i], r.y.v[4 * i + 1], r.y.v[4 * i + 2], r.y.v[4 * i + 3]);
 }
 
-// MODE 0: histogram of bucket sizes; 1: scatter (table index | sign) into bucket order;
-// 2: scatter the POINTS themselves (sign applied) into bucket order - the table is read
-// coalesced (thread = column) and the random side of the permutation is a write, so the
-// kernels that follow stream their inputs instead of gathering them.
+// MODE 0: histogram of bucket sizes; 1: scatter (table index | sign) into bucket order.
+// (Scattering the points themselves, so that later kernels stream instead of gather, was
+// measured: 1.5 ms of random 96-byte writes per 2^20 MSM, slower than the gathers it saves.)
 template <int MODE>
 __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -100,13 +97,7 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
         } else {
             uint32_t slot = atomicAdd(a.counts + bucket, 1u);
             uint32_t idx = a.tabulated ? (row * a.nwin + (uint32_t)w) * a.stride + col : row * a.stride + col;
-            if (MODE == 1) {
-                a.sorted[slot] = idx | ((neg ^ sneg) << 31);
-            } else {
-                G1Affine p = ldg_affine(a.pts + idx);
-                if (neg ^ sneg) p.y = fe_neg<FpParams>(p.y);
-                st_affine(a.sorted_pts + slot, p);
-            }
+            a.sorted[slot] = idx | ((neg ^ sneg) << 31);
         }
     }
 }
@@ -176,6 +167,16 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
     return r;
 }
 
+// point i (bit 31 = negate) of an array with `stride` bytes per point
+__device__ __forceinline__ const G1Affine* point_at(const char* pts, uint32_t stride, uint32_t i) {
+    return reinterpret_cast<const G1Affine*>(pts + (size_t)(i & 0x7fffffffu) * stride);
+}
+__device__ __forceinline__ G1Affine load_point(const char* pts, uint32_t stride, uint32_t i) {
+    G1Affine p = ldg_affine(point_at(pts, stride, i));
+    if (i >> 31) p.y = fe_neg<FpParams>(p.y);
+    return p;
+}
+
 // ---- batched-affine halving rounds.  A mixed XYZZ addition costs 10 Fp multiplies;
 // an AFFINE addition costs 3 once 1/(x2 - x1) is known, and Montgomery's trick turns
 // P inversions into one inversion plus 3(P-1) multiplies.  One round replaces every
@@ -190,7 +191,8 @@ __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p) {
 //   pass 2  walks the slots backwards, peels off each pair's inverse and writes the sum.
 // After a few rounds the survivors (a few per bucket) go through the XYZZ kernel below.
 struct RoundArgs {
-    const G1Affine* pts;      // GATHER: the resident table; else the previous round's output (bucket order)
+    const char* pts;          // GATHER: the resident table; else the previous round's output (bucket order)
+    uint32_t stride;          // bytes per input point (128 in a table, 96 otherwise)
     const uint32_t* off_out;  // [nbuckets + 1] bucket offsets of the output, off_out[b+1]-off_out[b] = ceil(count_in/2)
     uint32_t nbuckets;
     G1Affine* out;
@@ -198,6 +200,8 @@ struct RoundArgs {
     const uint32_t* where;    // streamed: [slot] first input index | (has a second point) << 31
     const uint2* where2;      // GATHER:   [slot] (table index | sign << 31) of both points, .y = kNone if single
     uint32_t p_max;           // steps per thread the scratch was sized for
+    G1Affine* stage;          // GATHER: [step][thread][2] the two points of each slot, parked by pass 1
+    Fp* inv;                  // [thread] inverse of the thread's running product (pass 1 -> pass 2)
 };
 
 constexpr uint32_t kMinSlots = 16;
@@ -232,22 +236,7 @@ __device__ __forceinline__ uint2 slot_desc(const RoundArgs& a, uint32_t o) {
     return make_uint2(e, (w >> 31) ? e + 1 : kNone);
 }
 
-__device__ __forceinline__ void prefetch_point(const G1Affine* p) {
-    const char* c = reinterpret_cast<const char*>(p);
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(c));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(c + 95));
-}
-__device__ __forceinline__ void prefetch_slot(const RoundArgs& a, uint2 d) {
-    prefetch_point(a.pts + (d.x & 0x7fffffffu));
-    if (d.y != kNone) prefetch_point(a.pts + (d.y & 0x7fffffffu));
-}
 
-// point i (bit 31 = negate) of the input
-__device__ __forceinline__ G1Affine load_point(const G1Affine* pts, uint32_t i) {
-    G1Affine p = ldg_affine(pts + (i & 0x7fffffffu));
-    if (i >> 31) p.y = fe_neg<FpParams>(p.y);
-    return p;
-}
 
 __device__ __forceinline__ Fp ldg_fp(const Fp* p) {
     const uint4* q = reinterpret_cast<const uint4*>(p);
@@ -281,13 +270,13 @@ __device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2,
 // denominator of a slot from the x coordinates alone; the y coordinates are fetched only
 // when a special case is possible (x == 0 may be the identity (0,0); equal x is a doubling
 // or a cancellation)
-__device__ __forceinline__ Fp slot_den(const G1Affine* pts, uint2 d) {
+__device__ __forceinline__ Fp slot_den(const char* pts, uint32_t stride, uint2 d) {
     using F = FpParams;
     if (d.y == kNone) return Fp::one();
-    Fp x1 = ldg_fp(&pts[d.x & 0x7fffffffu].x), x2 = ldg_fp(&pts[d.y & 0x7fffffffu].x);
+    Fp x1 = ldg_fp(&point_at(pts, stride, d.x)->x), x2 = ldg_fp(&point_at(pts, stride, d.y)->x);
     Fp dx = fe_sub<F>(x2, x1);
     if (x1.is_zero() || x2.is_zero() || dx.is_zero()) {
-        G1Affine p1 = load_point(pts, d.x), p2 = load_point(pts, d.y);
+        G1Affine p1 = load_point(pts, stride, d.x), p2 = load_point(pts, stride, d.y);
         Fp den;
         (void)pair_kind(p1, p2, true, den);
         return den;
@@ -326,60 +315,88 @@ __device__ __forceinline__ Fp warp_batch_inverse(const Fp& t) {
 }
 
 // A warp owns 32*P consecutive output slots; at step j lane l works on slot
-// base + 32*j + l, so the slot map, the points (2 x 96 B per lane, neighbouring lanes
-// neighbouring pairs) and the results are read and written as contiguous runs.
-template <bool GATHER>
-__global__ void __launch_bounds__(128, 4) k_affine_round(RoundArgs a) {
-    using F = FpParams;
+// base + 32*j + l, so the slot map, the streamed points (2 x 96 B per lane, neighbouring
+// lanes neighbouring pairs) and the results are read and written as contiguous runs.
+struct WarpSlots {
+    uint32_t base, cnt;  // first slot of the warp; steps of this lane
+};
+__device__ __forceinline__ bool warp_slots(const RoundArgs& a, uint32_t O, WarpSlots& ws) {
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t O = a.off_out[a.nbuckets];
     uint32_t P = (O + nt - 1) / nt;
     if (P < kMinSlots) P = kMinSlots;
     if (P > a.p_max) P = a.p_max;  // cannot happen: p_max comes from an upper bound on O
-    const uint64_t base64 = (uint64_t)(t >> 5) * 32u * P;  // first slot of this warp
-    if (base64 >= O) return;                                // whole warp idle
-    const uint32_t base = (uint32_t)base64;
+    const uint64_t base64 = (uint64_t)(t >> 5) * 32u * P;
+    if (base64 >= O) return false;  // whole warp idle
     // steps of this lane: slots base + 32*j + lane < end = min(O, base + 32*P).
     // NB: written as min(O - base, 32*P), ptxas 12.9 (sm_100a) fuses the subtraction and the min into
     // VIADDMNMX.U32 with the negation of `base` dropped (seen on B200 as out-of-range slots); the
     // add-then-min form below is what that instruction really computes.
-    uint64_t end64 = base64 + 32ull * P;
+    const uint64_t end64 = base64 + 32ull * P;
     const uint32_t end = end64 < O ? (uint32_t)end64 : O;
-    const uint32_t avail = end - base;  // >= 1
-    const uint32_t cnt = avail > lane ? (avail - lane + 31u) / 32u : 0u;
+    ws.base = (uint32_t)base64;
+    const uint32_t avail = end - ws.base;  // >= 1
+    ws.cnt = avail > lane ? (avail - lane + 31u) / 32u : 0u;
+    return true;
+}
 
-    // ---- pass 1: running product of the denominators
+// Pass 1 (+ the warp's inversion).  Few live registers, so it runs at a higher occupancy than
+// pass 2: it is the latency-bound half (GATHER: two random 128-byte lines per slot).  With
+// GATHER it also parks both points (sign applied; identity when the slot has one input) in
+// `stage`, [step][thread], so that pass 2 streams them instead of gathering them again.
+template <bool GATHER>
+__global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
+    using F = FpParams;
+    const uint32_t nt = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31;
+    WarpSlots ws;
+    if (!warp_slots(a, a.off_out[a.nbuckets], ws)) return;
     Fp run = Fp::one();
-    uint2 dn = make_uint2(0u, kNone);  // descriptor of the next step, fetched (and its points prefetched) one step ahead
-    if (cnt) dn = slot_desc<GATHER>(a, base + lane);
-    for (uint32_t j = 0; j < cnt; j++) {
-        const uint2 d = dn;
-        if (j + 1 < cnt) {
-            dn = slot_desc<GATHER>(a, base + 32u * (j + 1) + lane);
-            if (GATHER) prefetch_slot(a, dn);
+    for (uint32_t j = 0; j < ws.cnt; j++) {
+        const uint2 d = slot_desc<GATHER>(a, ws.base + 32u * j + lane);
+        Fp den;
+        if (GATHER) {
+            G1Affine p1 = load_point(a.pts, a.stride, d.x);
+            G1Affine p2 = d.y != kNone ? load_point(a.pts, a.stride, d.y) : G1Affine::inf();
+            (void)pair_kind(p1, p2, true, den);
+            G1Affine* st = a.stage + ((size_t)j * nt + t) * 2;
+            st_affine(st, p1);
+            st_affine(st + 1, p2);
+        } else {
+            den = slot_den(a.pts, a.stride, d);
         }
-        Fp den = slot_den(a.pts, d);
         run = fe_mul<F>(run, den);
         a.pref[(size_t)j * nt + t] = run;
     }
-    // ---- one inversion per warp
-    Fp inv = warp_batch_inverse(run);
-    // ---- pass 2: peel the inverses off backwards, add
-    if (cnt) dn = slot_desc<GATHER>(a, base + 32u * (cnt - 1) + lane);
-    for (uint32_t j = cnt; j-- > 0;) {
-        const uint32_t o = base + 32u * j + lane;
-        const uint2 d = dn;
-        if (j) {
-            dn = slot_desc<GATHER>(a, o - 32u);
-            if (GATHER) prefetch_slot(a, dn);
+    a.inv[t] = warp_batch_inverse(run);
+}
+
+// Pass 2: peel the inverses off backwards and add.
+template <bool STAGED>
+__global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
+    using F = FpParams;
+    const uint32_t nt = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31;
+    WarpSlots ws;
+    if (!warp_slots(a, a.off_out[a.nbuckets], ws)) return;
+    Fp inv = a.inv[t];
+    for (uint32_t j = ws.cnt; j-- > 0;) {
+        const uint32_t o = ws.base + 32u * j + lane;
+        G1Affine p1, p2;
+        if (STAGED) {
+            const G1Affine* st = a.stage + ((size_t)j * nt + t) * 2;
+            p1 = ldg_affine(st);
+            p2 = ldg_affine(st + 1);
+        } else {
+            const uint2 d = slot_desc<false>(a, o);
+            p1 = load_point(a.pts, a.stride, d.x);
+            p2 = d.y != kNone ? load_point(a.pts, a.stride, d.y) : G1Affine::inf();
         }
-        const bool has2 = d.y != kNone;
-        G1Affine p1 = load_point(a.pts, d.x);
-        G1Affine p2 = has2 ? load_point(a.pts, d.y) : G1Affine::inf();
         Fp den;
-        const int kind = pair_kind(p1, p2, has2, den);
+        const int kind = pair_kind(p1, p2, true, den);
         Fp dinv = inv;
         if (j) dinv = fe_mul<F>(inv, a.pref[(size_t)(j - 1) * nt + t]);
         inv = fe_mul<F>(inv, den);
@@ -430,7 +447,8 @@ __device__ __forceinline__ uint32_t chunk_len(uint32_t E, uint32_t nt) {
 }
 
 template <int MINB, bool DIRECT>  // DIRECT: pts[e] is entry e itself (output of the affine rounds), no gather, no sign
-__global__ void __launch_bounds__(128, MINB) k_accumulate(const G1Affine* __restrict__ pts, const uint32_t* __restrict__ sorted,
+__global__ void __launch_bounds__(128, MINB) k_accumulate(const char* __restrict__ pts, uint32_t stride,
+                                                          const uint32_t* __restrict__ sorted,
                                                           const uint32_t* __restrict__ offsets, uint32_t nbuckets,
                                                           G1Xyzz* __restrict__ partial) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -460,13 +478,8 @@ __global__ void __launch_bounds__(128, MINB) k_accumulate(const G1Affine* __rest
             } while (next <= e);
         }
         G1Affine p;
-        if (DIRECT) {
-            p = ldg_affine(pts + e);
-        } else {
-            uint32_t ent = sorted[e];
-            p = ldg_affine(pts + (ent & 0x7fffffffu));
-            if (ent >> 31) p.y = fe_neg<FpParams>(p.y);
-        }
+        if (DIRECT) p = ldg_affine(point_at(pts, stride, e));
+        else p = load_point(pts, stride, sorted[e]);
         g1_add_mixed(acc, p);
     }
     partial[cb + t] = acc;
@@ -652,16 +665,22 @@ __global__ void __launch_bounds__(64) k_window_combine(const G1Xyzz* __restrict_
 // are produced by repeated doubling in XYZZ, parked in the output slots, and brought
 // back to affine with ONE field inversion per point (Montgomery's trick across the
 // windows of that point).
-__global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict__ in, G1Affine* __restrict__ out, size_t n,
+struct alignas(128) G1TableEntry {  // kTableStride bytes: x | y | 32 bytes of padding
+    G1Affine p;
+    uint32_t pad[8];
+};
+static_assert(sizeof(G1TableEntry) == kTableStride, "table entries are one 128-byte line");
+
+__global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict__ in, G1TableEntry* __restrict__ out, size_t n,
                                                      size_t rows, int c, int nwin, G1Xyzz* __restrict__ park) {
     size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * rows) return;
     size_t row = t / n, k = t - row * n;
     G1Affine p = in[t];
-    G1Affine* o = out + row * (size_t)nwin * n + k;  // window stride n
-    o[0] = p;
+    G1TableEntry* o = out + row * (size_t)nwin * n + k;  // window stride n
+    o[0].p = p;
     if (p.is_inf()) {
-        for (int w = 1; w < nwin; w++) o[(size_t)w * n] = p;
+        for (int w = 1; w < nwin; w++) o[(size_t)w * n].p = p;
         return;
     }
     G1Xyzz* pk = park + t;  // window stride n*rows
@@ -679,7 +698,7 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
     for (int w = nwin - 1; w >= 1; w--) {
         G1Xyzz s = pk[(size_t)(w - 1) * ps];
         Fp izzz = fe_mul<FpParams>(inv, pre[w - 1]);
-        o[(size_t)w * n] = g1_to_affine_with_inv(s, izzz);
+        o[(size_t)w * n].p = g1_to_affine_with_inv(s, izzz);
         inv = fe_mul<FpParams>(inv, s.zzz);
     }
 }
@@ -688,16 +707,17 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
 
 int msm_num_windows(int c) { return (255 + c - 1) / c; }  // scalars are recoded below 2^254 (k_digits)
 
-// Window width by a cost model in Fp multiplications: n*W mixed additions (10 each)
-// plus 2 full additions (14 each) per bucket; without a table every window has its own
-// bucket set and the windows are joined by a doubling ladder.
+// Window width by a cost model in Fp multiplications: n*W mixed additions (10 each) plus
+// 60 per bucket (2 full additions of 14, doubled: the reduction kernels are short and
+// latency-bound; calibrated on the measured window sweep, profiles/r1_v2_window_sweep.jsonl);
+// without a table every window has its own bucket set and a doubling ladder joins them.
 int msm_pick_window(size_t n, bool tabulated) {
     int best = 4;
     double best_cost = 1e300;
     for (int c = 4; c <= 22; c++) {
         const double W = (double)msm_num_windows(c);
         const double buckets = (double)((size_t)1 << (c - 1)) * (tabulated ? 1.0 : W);
-        double cost = (double)n * W * 10.0 + buckets * 28.0;
+        double cost = (double)n * W * 10.0 + buckets * 60.0;
         if (!tabulated) cost += 255.0 * 9.0;
         if (cost < best_cost) {
             best_cost = cost;
@@ -707,9 +727,10 @@ int msm_pick_window(size_t n, bool tabulated) {
     return best;
 }
 
-void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, G1Affine* d_out, DevBuf& scratch,
+void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, void* d_out_v, DevBuf& scratch,
                      cudaStream_t st) {
     if (!n || !rows) return;
+    G1TableEntry* d_out = static_cast<G1TableEntry*>(d_out_v);
     // chunk the rows so the XYZZ parking area stays below ~2 GiB
     size_t per_row = (size_t)(nwin - 1) * n * sizeof(G1Xyzz);
     size_t chunk = per_row ? ((size_t)2 << 30) / per_row : rows;
@@ -758,13 +779,13 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     if (rounds_env == -2) {
         const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
         rounds_env = e ? atoi(e) : -1;
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_affine_round<true>, 128, 0));
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2<true>, 128, 0));
         if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
     }
-    // Measured on B200 (profiles/r1_v3_*): the first round gathers every point twice (6.6 GB of
-    // random 96-byte reads at ~2 TB/s) and ends up no faster than the XYZZ kernel, the later,
-    // streamed rounds run at ~78% of the multiplier peak.  Off by default until the gather is fixed.
-    int rounds = rounds_env >= 0 ? rounds_env : 0;
+    // Measured on B200 (profiles/): three rounds ahead of the XYZZ kernel are ~8% faster than the
+    // XYZZ kernel alone at 2^20 points (pass 2 runs at the multiplier's rate, pass 1 of the first
+    // round is bound by the gather); small inputs do not amortise the per-round inversion.
+    int rounds = rounds_env >= 0 ? rounds_env : ((entries >= (4u << 20) && entries / nbuckets >= 8) ? 3 : 0);
     if (rounds > 8) rounds = 8;
     uint32_t* sorted = s.sorted.as<uint32_t>(entries);
 
@@ -782,8 +803,6 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     a.buckets_per_win = bpw;
     a.counts = counts;
     a.sorted = sorted;
-    a.pts = bases.pts;
-    a.sorted_pts = nullptr;  // MODE 2 (scatter the points, not their indices) measured slower: 1.5 ms of random 96-B writes
     DigitArgs a2 = a;
     const unsigned gb = (unsigned)((n + 255) / 256);
     (++fb::g_launches, k_digits<0><<<gb, 256, 0, st>>>(a));
@@ -796,7 +815,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
 
     // batched-affine halving rounds, then XYZZ accumulation of the survivors
     const uint32_t* off_cur = offsets;
-    const G1Affine* pts_cur = bases.pts;   // round 0 gathers from the table through `sorted`
+    const char* pts_cur = static_cast<const char*>(bases.pts);  // round 0 gathers from the table through `sorted`
+    uint32_t stride_cur = bases.stride();
     uint64_t ub = entries;                 // upper bound on the number of live points
     if (rounds > 0) prof_mark("msm.affine_rounds", st);
     for (int r = 0; r < rounds; r++) {
@@ -813,6 +833,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         const uint32_t rnt = blocks * 128;
         RoundArgs ra;
         ra.pts = pts_cur;
+        ra.stride = stride_cur;
         ra.off_out = off_out;
         ra.nbuckets = nbuckets;
         ra.out = ((r & 1) ? s.pts_b : s.pts_a).as<G1Affine>(ub_out);
@@ -825,14 +846,20 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         ra.where2 = reinterpret_cast<const uint2*>(wbuf);
         uint64_t mb = (ub_out + 255) / 256;
         if (mb > 4u * kNumSMs * 8u) mb = 4u * kNumSMs * 8u;
+        ra.inv = s.inv.as<Fp>(rnt);
+        ra.stage = nullptr;
         if (r == 0) {
+            ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
             (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
-            (++fb::g_launches, k_affine_round<true><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass1<true><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass2<true><<<blocks, 128, 0, st>>>(ra));
         } else {
             (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
-            (++fb::g_launches, k_affine_round<false><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass1<false><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass2<false><<<blocks, 128, 0, st>>>(ra));
         }
-        pts_cur = ra.out;
+        pts_cur = reinterpret_cast<const char*>(ra.out);
+        stride_cur = (uint32_t)sizeof(G1Affine);
         off_cur = off_out;
         ub = ub_out;
     }
@@ -851,8 +878,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     }
     const uint32_t nt = acc_blocks * 128;
     G1Xyzz* partial = s.seg_t.as<G1Xyzz>((size_t)nbuckets + nt);
-    if (rounds > 0) (++fb::g_launches, k_accumulate<4, true><<<acc_blocks, 128, 0, st>>>(pts_cur, nullptr, off_cur, nbuckets, partial));
-    else (++fb::g_launches, k_accumulate<4, false><<<acc_blocks, 128, 0, st>>>(bases.pts, sorted, offsets, nbuckets, partial));
+    if (rounds > 0) (++fb::g_launches, k_accumulate<4, true><<<acc_blocks, 128, 0, st>>>(pts_cur, stride_cur, nullptr, off_cur, nbuckets, partial));
+    else (++fb::g_launches, k_accumulate<4, false><<<acc_blocks, 128, 0, st>>>(pts_cur, stride_cur, sorted, offsets, nbuckets, partial));
     const uint32_t* offsets_final = off_cur;
     prof_mark("msm.combine", st);
     uint32_t* long_list = s.order.as<uint32_t>((size_t)nt + 2);
