@@ -90,7 +90,7 @@ def own_arm(args):
     import torch
     import torch.distributed as dist
 
-    from fourier_b200 import PianoBackend, synth
+    from fourier_b200 import PianoBackend, shard, synth
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -111,8 +111,7 @@ def own_arm(args):
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     be.set_stream(stream.cuda_stream)
-    ncols = T // world
-    col0 = rank * ncols
+    col0, ncols = shard.split_range(T, world, rank)  # this rank's point (column) range of the MSM
     if world > 1:
         be.set_col_shard(col0, ncols)
     t0 = time.time()

@@ -138,11 +138,10 @@ def run_ntt(args):
 # ------------------------------------------------------------------ config 4: one big MSM
 def run_msm(args):
     torch, dist, rank, world, local, dev, stream = _env()
-    from fourier_b200 import PianoBackend, synth
+    from fourier_b200 import PianoBackend, shard, synth
     lg = int(os.environ.get("FB_MSM_LOG", "24"))
     n = 1 << lg
-    per = n // world
-    start = rank * per
+    start, per = shard.split_range(n, world, rank)  # this rank's point range
     be = PianoBackend(10, 0, device=local)
     be.set_stream(stream.cuda_stream)
     t0 = time.time()
@@ -251,12 +250,11 @@ def run_msm(args):
 # ------------------------------------------------------------------ config 5: bivariate rows
 def run_bipoly(args):
     torch, dist, rank, world, local, dev, stream = _env()
-    from fourier_b200 import PianoBackend, synth
+    from fourier_b200 import PianoBackend, shard, synth
     n_scale = int(os.environ.get("FB_BIPOLY_SCALE", "22"))
     m_scale = int(os.environ.get("FB_BIPOLY_MSCALE", "10"))
     M, T = 1 << m_scale, 1 << (n_scale - m_scale)
-    rows = M // world
-    row0 = rank * rows
+    row0, rows = shard.split_range(M, world, rank)  # this rank's rows (M and world are powers of two: equal shares)
     be = PianoBackend(n_scale, m_scale, device=local, window_bits=int(os.environ.get("FB_BENCH_WINDOW", "0")))
     be.set_stream(stream.cuda_stream)
     t0 = time.time()
@@ -279,13 +277,8 @@ def run_bipoly(args):
             dist.all_gather_into_tensor(gathered, d_out)
 
     def unpack(buf: bytes):
-        cs, ys, ps = [], [], []
-        for k in range(world):
-            blk = buf[k * rows * 128:(k + 1) * rows * 128]
-            cs += [blk[i * 48:(i + 1) * 48] for i in range(rows)]
-            ys += [blk[rows * 48 + i * 32:rows * 48 + (i + 1) * 32] for i in range(rows)]
-            ps += [blk[rows * 80 + i * 48:rows * 80 + (i + 1) * 48] for i in range(rows)]
-        return cs, ys, ps
+        blobs = [buf[k * rows * 128:(k + 1) * rows * 128] for k in range(world)]
+        return shard.unpack_rows(blobs, [rows] * world)
 
     for _ in range(max(args.warmup, 3)):
         step_device()
@@ -308,7 +301,7 @@ def run_bipoly(args):
     def step_host():
         c = be.commit_rows(row0, rows, h_coeffs)
         y, p = be.open_rows(row0, rows, h_coeffs, alpha_b)
-        blob = b"".join(c) + b"".join(y) + b"".join(p)
+        blob = shard.pack_rows(c, y, p)
         if world > 1:
             mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
             dist.all_gather_into_tensor(gathered, mine)
