@@ -69,3 +69,11 @@ class ClockSampler:
         os.unlink(self.f.name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def load_traffic():
+    """{phase: dram bytes per MSM} from the committed ncu --set full capture (profiles/traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        return {k: v for k, v in json.load(open(p)).items() if not k.startswith("_")}
+    return {}

@@ -818,8 +818,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     const char* pts_cur = static_cast<const char*>(bases.pts);  // round 0 gathers from the table through `sorted`
     uint32_t stride_cur = bases.stride();
     uint64_t ub = entries;                 // upper bound on the number of live points
-    if (rounds > 0) prof_mark("msm.affine_rounds", st);
     for (int r = 0; r < rounds; r++) {
+        prof_mark("msm.round_map", st);
         const uint64_t ub_out = (ub + nbuckets) / 2 + 1;
         uint32_t* cnt_tmp = s.order.as<uint32_t>(nbuckets + 1);
         uint32_t* off_out = (r & 1) ? cursor : counts;
@@ -851,11 +851,15 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         if (r == 0) {
             ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
             (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
+            prof_mark("msm.round_pass1", st);
             (++fb::g_launches, k_round_pass1<true><<<blocks, 128, 0, st>>>(ra));
+            prof_mark("msm.round_pass2", st);
             (++fb::g_launches, k_round_pass2<true><<<blocks, 128, 0, st>>>(ra));
         } else {
             (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
+            prof_mark("msm.round_pass1", st);
             (++fb::g_launches, k_round_pass1<false><<<blocks, 128, 0, st>>>(ra));
+            prof_mark("msm.round_pass2", st);
             (++fb::g_launches, k_round_pass2<false><<<blocks, 128, 0, st>>>(ra));
         }
         pts_cur = reinterpret_cast<const char*>(ra.out);
