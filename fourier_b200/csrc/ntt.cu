@@ -109,7 +109,44 @@ __device__ __forceinline__ Fr ldg_fr(const Fr* p) {
     return r;
 }
 
-__global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
+// One group of G DIF stages (s_hi .. s_hi-G+1) over the staged tile.  A work item is the set of
+// 2^G rows  base | (m << s_lo)  (m < 2^G; base has zero bits in [s_lo, s_hi]) of one column.
+template <int G>
+__device__ __forceinline__ void ntt_group(uint4* s0, uint4* s1, const uint4* t0, const uint4* t1, int s_hi, int log_r, int log_b,
+                                          uint32_t tile, uint32_t tid, uint32_t nt) {
+    constexpr int M = 1 << G;
+    const int s_lo = s_hi - G + 1;
+    const uint32_t B = 1u << log_b;
+    for (uint32_t q = tid; q < (tile >> G); q += nt) {
+        const uint32_t cb = q & (B - 1), qr = q >> log_b;
+        const uint32_t low = qr & ((1u << s_lo) - 1u);
+        const uint32_t base = ((qr >> s_lo) << (s_hi + 1)) | low;
+        Fr x[M];
+#pragma unroll
+        for (int m = 0; m < M; m++) x[m] = lds_fr(s0, s1, ((base | ((uint32_t)m << s_lo)) << log_b) | cb);
+#pragma unroll
+        for (int t = G - 1; t >= 0; t--) {
+            const int st = s_lo + t;  // stage: rows m and m + 2^t differ in bit st
+#pragma unroll
+            for (int m = 0; m < M; m++) {
+                if (m & (1 << t)) continue;
+                Fr u = x[m], v = x[m | (1 << t)];
+                x[m] = fe_add<FrParams>(u, v);
+                Fr dif = fe_sub<FrParams>(u, v);
+                if (st > 0) {
+                    // twiddle w_R^(j * 2^(log_r-1-st)),  j = row index mod 2^st
+                    const uint32_t j = low | ((uint32_t)(m & ((1 << t) - 1)) << s_lo);
+                    dif = fe_mul<FrParams>(dif, lds_fr(t0, t1, j << (log_r - 1 - st)));
+                }
+                x[m | (1 << t)] = dif;
+            }
+        }
+#pragma unroll
+        for (int m = 0; m < M; m++) sts_fr(s0, s1, ((base | ((uint32_t)m << s_lo)) << log_b) | cb, x[m]);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_ntt_pass(PassArgs a) {
     extern __shared__ uint4 smem[];
     const uint32_t R = 1u << a.log_r, B = 1u << a.log_b;
     const uint32_t tile = R << a.log_b;
@@ -135,22 +172,17 @@ __global__ void __launch_bounds__(512) k_ntt_pass(PassArgs a) {
     }
     __syncthreads();
 
-    // radix-2 decimation-in-frequency stages: natural in, bit-reversed out
-    for (int s = a.log_r - 1; s >= 0; s--) {
-        const uint32_t h = 1u << s;
-        for (uint32_t p = tid; p < (tile >> 1); p += nt) {
-            uint32_t cb = p & (B - 1), pr = p >> a.log_b;
-            uint32_t j = pr & (h - 1);
-            uint32_t i = ((pr >> s) << (s + 1)) | j;
-            uint32_t e0 = (i << a.log_b) | cb, e1 = e0 + (h << a.log_b);
-            Fr u = lds_fr(s0, s1, e0), v = lds_fr(s0, s1, e1);
-            Fr sum = fe_add<FrParams>(u, v);
-            Fr dif = fe_sub<FrParams>(u, v);
-            if (s > 0) dif = fe_mul<FrParams>(dif, lds_fr(t0, t1, j << (a.log_r - 1 - s)));
-            sts_fr(s0, s1, e0, sum);
-            sts_fr(s0, s1, e1, dif);
-        }
+    // radix-2 decimation-in-frequency stages (natural in, bit-reversed out), taken in groups of up
+    // to 3: a thread pulls the 2^g rows that interact over the group's stages into registers,
+    // runs the g stages there and writes them back - one shared-memory round trip and one
+    // barrier per group instead of per stage.
+    for (int s_hi = a.log_r - 1; s_hi >= 0;) {
+        const int g = s_hi >= 2 ? 3 : s_hi + 1;
+        if (g == 3) ntt_group<3>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+        else if (g == 2) ntt_group<2>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+        else ntt_group<1>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
         __syncthreads();
+        s_hi -= g;
     }
 
     const uint32_t lo_mask = (1u << a.lo_bits) - 1;
@@ -269,6 +301,9 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         a.log_b = kTileLog - a.log_r;
         if (a.log_b > log_c) a.log_b = log_c;
         if (a.log_b > 3) a.log_b = 3;
+        // enough tiles per SM that the last, partial wave is short (2^20 = 1024 x 1024: 512 tiles of 2 columns
+        // leave 4 tiles on some SMs and 3 on others; 1024 tiles of one column balance to 7 vs 6.9)
+        while (a.log_b > 0 && ((a.C * batch) >> a.log_b) < 8ull * kNumSMs) a.log_b--;
         a.log_q = log_q;
         a.lo_bits = tab.lo_bits;
         bool last = (j == plan.npass - 1);
@@ -286,7 +321,7 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         else dst = out;
         a.out = dst;
         uint32_t tile = 1u << (a.log_r + a.log_b);
-        uint32_t threads = tile / 2 < 32 ? 32 : (tile / 2 > 512 ? 512 : tile / 2);
+        uint32_t threads = tile / 8 < 32 ? 32 : (tile / 8 > 256 ? 256 : tile / 8);
         size_t smem = (size_t)tile * 32 + ((size_t)1 << a.log_r) * 16;
         unsigned long long blocks = a.C >> a.log_b;
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
