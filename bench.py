@@ -241,8 +241,8 @@ def own_arm(args):
                        "parallelism": "1 GPU" if world == 1 else "MSM point ranges over %d GPUs + all-gather of 224-byte partials" % world,
                        "l2": "inputs larger than L2: window tables %.2f GB per GPU + 32 MiB coefficients" %
                              (table_windows * ncols * 128 / 1e9), "window_bits": wbits, "srs_setup_s": round(setup_s, 2), "seed": [SEED_COEFFS, SEED_ALPHA]},
-            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * n * 32 + 32, "d2h_bytes_per_step": 48 + 32 + 48
-                    if world == 1 else 96 + 32 + 96 + world * 224},
+            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": (2 * n if world == 1 else n + ncols) * 32 + 32,
+                    "d2h_bytes_per_step": 48 + 32 + 48 if world == 1 else 96 + 32 + 96 + world * 224},
             "gpu_launches": int(launches),
             "clocks": clk,
             "roofline": {"kernel": PHASE_KERNELS.get(dom, dom), "bound": "hbm",

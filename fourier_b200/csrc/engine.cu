@@ -565,7 +565,19 @@ int fb_dev_worker_open_partial(fb_ctx* c, uint64_t i, const void* d_coeffs, uint
 int fb_worker_commit_partial(fb_ctx* c, uint64_t i, const uint8_t* coeffs_be, uint64_t len, uint8_t out96[96]) {
     return ctx_call(c, [&]() -> int {
         ctx_reset_err(c);
-        Fr* d_s = ctx_upload_fr(c, c->in_bytes, c->fr_a, coeffs_be, len);
+        // only the resident column range of the coefficients takes part in this shard's MSM: upload
+        // that slice (at its own offset, so the indices line up) instead of the whole row
+        // NB: scalars outside the slice are therefore not range-checked by this shard; the shard
+        // that owns them rejects them ("Invalid scalar").
+        const uint64_t lo = c->col0 < len ? c->col0 : len;
+        const uint64_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
+        Fr* d_s = c->fr_a.as<Fr>(len + 1);
+        if (hi > lo) {
+            uint8_t* d_b = c->in_bytes.as<uint8_t>((hi - lo) * 32 + 32);
+            prof_mark("h2d", c->stream);
+            FB_CUDA(cudaMemcpyAsync(d_b, coeffs_be + lo * 32, (hi - lo) * 32, cudaMemcpyHostToDevice, c->stream));
+            fr_from_be(d_b, d_s + lo, hi - lo, c->d_err, c->stream);
+        }
         uint8_t* d_ob = c->out_bytes.as<uint8_t>(128);
         int rc = dev_commit(c, i, d_s, len, d_ob, 96);
         if (rc) return rc;
