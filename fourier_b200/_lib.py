@@ -34,6 +34,10 @@ SYMBOLS = [
     ("fb_open_rows", C.c_int, [_ctx, C.c_uint64, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p]),
     ("fb_master_commit", C.c_int, [_ctx, _u8p, C.c_uint64, _u8p]),
     ("fb_master_open", C.c_int, [_ctx, _u8p, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
+    ("fb_worker_verify", C.c_int, [_ctx, C.c_uint64, _u8p, _u8p, _u8p, _u8p, C.POINTER(C.c_int)]),
+    ("fb_master_verify", C.c_int, [_ctx, _u8p, _u8p, _u8p, _u8p, _u8p, _u8p, C.POINTER(C.c_int)]),
+    ("fb_pairing_check", C.c_int, [_u8p, _u8p, C.c_uint64, C.POINTER(C.c_int)]),
+    ("fb_pairing_value", C.c_int, [_u8p, _u8p, C.c_uint64, _u8p]),
     ("fb_fft", C.c_int, [_ctx, C.c_int, C.c_int, _u8p, C.c_uint64, _u8p]),
     ("fb_evaluate", C.c_int, [_ctx, _u8p, C.c_uint64, _u8p, _u8p]),
     ("fb_bases_from_points", C.c_int, [_ctx, _u8p, C.c_uint64, C.c_int, C.POINTER(_bases)]),

@@ -6,6 +6,12 @@
 // multiplications on the twist  y^2 = x^3 + 4(1+u)  over Fp2 = Fp[u]/(u^2+1) do
 // not justify a kernel, so they run here on the same Montgomery field code as the
 // device (field.cuh compiled for the host).
+//
+// The second half of the file is the pairing check behind worker_verify /
+// master_verify (piano.rs:358-388, 422-464: blst Pairing::raw_aggregate, final_exp,
+// blst_fp12_is_one): optimal-ate Miller loop on affine twist coordinates, tower
+// Fp12 = Fp6[w]/(w^2-v), Fp6 = Fp2[v]/(v^3-(1+u)), final exponentiation with the
+// (x-1)^2 (x+p)(x^2+p^2-1)+3 hard part.  A few pairings per verify call: host work.
 #include <string.h>
 
 #include <vector>
@@ -16,6 +22,65 @@ namespace fb {
 
 namespace {
 using F = FpParams;
+
+// Montgomery product on 6 x 64-bit limbs (the host has a 64x64->128 multiplier; the
+// 32-bit carry-chain code in field_mul.cuh is written for the GPU's integer pipe).
+// Same representation and the same fully reduced result as fe_mul<FpParams>.
+Fp fmul(const Fp& a, const Fp& b) {
+    typedef unsigned __int128 u128;
+    static const Fp mod = Fp::modulus();
+    static const uint64_t ninv = [] {
+        uint64_t m0, inv = 1;
+        memcpy(&m0, mod.v, 8);
+        for (int i = 0; i < 6; i++) inv *= 2 - m0 * inv;
+        return (uint64_t)0 - inv;
+    }();
+    uint64_t x[6], y[6], m[6], t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    memcpy(x, a.v, 48);
+    memcpy(y, b.v, 48);
+    memcpy(m, mod.v, 48);
+    for (int i = 0; i < 6; i++) {
+        u128 carry = 0;
+        for (int j = 0; j < 6; j++) {
+            u128 s = (u128)x[i] * y[j] + t[j] + carry;
+            t[j] = (uint64_t)s;
+            carry = s >> 64;
+        }
+        u128 s = (u128)t[6] + carry;
+        t[6] = (uint64_t)s;
+        t[7] = (uint64_t)(s >> 64);
+        uint64_t q = t[0] * ninv;
+        carry = ((u128)q * m[0] + t[0]) >> 64;
+        for (int j = 1; j < 6; j++) {
+            s = (u128)q * m[j] + t[j] + carry;
+            t[j - 1] = (uint64_t)s;
+            carry = s >> 64;
+        }
+        s = (u128)t[6] + carry;
+        t[5] = (uint64_t)s;
+        t[6] = t[7] + (uint64_t)(s >> 64);
+    }
+    bool ge = t[6] != 0;
+    if (!ge) {
+        ge = true;
+        for (int j = 5; j >= 0; j--)
+            if (t[j] != m[j]) {
+                ge = t[j] > m[j];
+                break;
+            }
+    }
+    if (ge) {
+        uint64_t borrow = 0;
+        for (int j = 0; j < 6; j++) {
+            u128 d = (u128)t[j] - m[j] - borrow;
+            t[j] = (uint64_t)d;
+            borrow = (uint64_t)(d >> 64) & 1;
+        }
+    }
+    Fp r;
+    memcpy(r.v, t, 48);
+    return r;
+}
 
 struct Fp2 {
     Fp a, b;  // a + b*u
@@ -28,16 +93,19 @@ Fp2 f2_add(const Fp2& x, const Fp2& y) { return Fp2{fe_add<F>(x.a, y.a), fe_add<
 Fp2 f2_sub(const Fp2& x, const Fp2& y) { return Fp2{fe_sub<F>(x.a, y.a), fe_sub<F>(x.b, y.b)}; }
 Fp2 f2_neg(const Fp2& x) { return Fp2{fe_neg<F>(x.a), fe_neg<F>(x.b)}; }
 Fp2 f2_mul(const Fp2& x, const Fp2& y) {
-    Fp aa = fe_mul<F>(x.a, y.a), bb = fe_mul<F>(x.b, y.b);
-    Fp cross = fe_mul<F>(fe_add<F>(x.a, x.b), fe_add<F>(y.a, y.b));
+    Fp aa = fmul(x.a, y.a), bb = fmul(x.b, y.b);
+    Fp cross = fmul(fe_add<F>(x.a, x.b), fe_add<F>(y.a, y.b));
     return Fp2{fe_sub<F>(aa, bb), fe_sub<F>(fe_sub<F>(cross, aa), bb)};
 }
-Fp2 f2_sqr(const Fp2& x) { return f2_mul(x, x); }
+Fp2 f2_sqr(const Fp2& x) {  // (a+b)(a-b) + 2ab u
+    Fp ab = fmul(x.a, x.b);
+    return Fp2{fmul(fe_add<F>(x.a, x.b), fe_sub<F>(x.a, x.b)), fe_dbl<F>(ab)};
+}
 Fp2 f2_dbl(const Fp2& x) { return f2_add(x, x); }
 Fp2 f2_inv(const Fp2& x) {
-    Fp nrm = fe_add<F>(fe_sqr<F>(x.a), fe_sqr<F>(x.b));
-    Fp i = fe_inv<F>(nrm);
-    return Fp2{fe_mul<F>(x.a, i), fe_neg<F>(fe_mul<F>(x.b, i))};
+    Fp nrm = fe_add<F>(fmul(x.a, x.a), fmul(x.b, x.b));
+    Fp i = fe_inv_gcd<F>(nrm);
+    return Fp2{fmul(x.a, i), fe_neg<F>(fmul(x.b, i))};
 }
 Fp fp_sqrt_candidate(const Fp& x) {
     constexpr uint32_t e[12] = {0xffffeaabu, 0xee7fbfffu, 0xac54ffffu, 0x07aaffffu, 0x3dac3d89u, 0xd9cc34a8u,
@@ -265,6 +333,170 @@ void secret_to_scalar(const uint8_t s[32], uint32_t k[8]) {  // big-endian bytes
     memcpy(k, x.v, 32);
 }
 
+// ================================================================= pairing
+// Fp6 = Fp2[v]/(v^3 - xi), xi = 1 + u;  Fp12 = Fp6[w]/(w^2 - v).  Read as a
+// polynomial in w (w^6 = xi) the coefficient of w^(2i) is a.c[i], of w^(2i+1) b.c[i].
+struct Fp6 {
+    Fp2 c[3];
+};
+struct Fp12 {
+    Fp6 a, b;
+};
+Fp2 f2_conj(const Fp2& x) { return Fp2{x.a, fe_neg<F>(x.b)}; }
+Fp2 f2_mul_xi(const Fp2& x) { return Fp2{fe_sub<F>(x.a, x.b), fe_add<F>(x.a, x.b)}; }  // (a+bu)(1+u)
+Fp2 f2_mul_fp(const Fp2& x, const Fp& s) { return Fp2{fmul(x.a, s), fmul(x.b, s)}; }
+
+Fp6 f6_zero() { return Fp6{{f2_zero(), f2_zero(), f2_zero()}}; }
+Fp6 f6_one() { return Fp6{{f2_one(), f2_zero(), f2_zero()}}; }
+Fp6 f6_add(const Fp6& x, const Fp6& y) { return Fp6{{f2_add(x.c[0], y.c[0]), f2_add(x.c[1], y.c[1]), f2_add(x.c[2], y.c[2])}}; }
+Fp6 f6_sub(const Fp6& x, const Fp6& y) { return Fp6{{f2_sub(x.c[0], y.c[0]), f2_sub(x.c[1], y.c[1]), f2_sub(x.c[2], y.c[2])}}; }
+Fp6 f6_neg(const Fp6& x) { return Fp6{{f2_neg(x.c[0]), f2_neg(x.c[1]), f2_neg(x.c[2])}}; }
+Fp6 f6_mul_v(const Fp6& x) { return Fp6{{f2_mul_xi(x.c[2]), x.c[0], x.c[1]}}; }
+bool f6_eq(const Fp6& x, const Fp6& y) { return f2_eq(x.c[0], y.c[0]) && f2_eq(x.c[1], y.c[1]) && f2_eq(x.c[2], y.c[2]); }
+Fp6 f6_mul(const Fp6& x, const Fp6& y) {  // Karatsuba, 6 Fp2 products
+    Fp2 v0 = f2_mul(x.c[0], y.c[0]), v1 = f2_mul(x.c[1], y.c[1]), v2 = f2_mul(x.c[2], y.c[2]);
+    Fp2 t12 = f2_sub(f2_sub(f2_mul(f2_add(x.c[1], x.c[2]), f2_add(y.c[1], y.c[2])), v1), v2);
+    Fp2 t01 = f2_sub(f2_sub(f2_mul(f2_add(x.c[0], x.c[1]), f2_add(y.c[0], y.c[1])), v0), v1);
+    Fp2 t02 = f2_sub(f2_sub(f2_mul(f2_add(x.c[0], x.c[2]), f2_add(y.c[0], y.c[2])), v0), v2);
+    return Fp6{{f2_add(v0, f2_mul_xi(t12)), f2_add(t01, f2_mul_xi(v2)), f2_add(t02, v1)}};
+}
+Fp6 f6_inv(const Fp6& x) {
+    Fp2 c0 = f2_sub(f2_sqr(x.c[0]), f2_mul_xi(f2_mul(x.c[1], x.c[2])));
+    Fp2 c1 = f2_sub(f2_mul_xi(f2_sqr(x.c[2])), f2_mul(x.c[0], x.c[1]));
+    Fp2 c2 = f2_sub(f2_sqr(x.c[1]), f2_mul(x.c[0], x.c[2]));
+    Fp2 t = f2_add(f2_mul(x.c[0], c0), f2_mul_xi(f2_add(f2_mul(x.c[2], c1), f2_mul(x.c[1], c2))));
+    Fp2 ti = f2_inv(t);
+    return Fp6{{f2_mul(c0, ti), f2_mul(c1, ti), f2_mul(c2, ti)}};
+}
+
+Fp12 f12_one() { return Fp12{f6_one(), f6_zero()}; }
+bool f12_is_one(const Fp12& x) { return f6_eq(x.a, f6_one()) && f6_eq(x.b, f6_zero()); }
+Fp12 f12_conj(const Fp12& x) { return Fp12{x.a, f6_neg(x.b)}; }  // x^(p^6): w -> -w
+Fp12 f12_mul(const Fp12& x, const Fp12& y) {
+    Fp6 aa = f6_mul(x.a, y.a), bb = f6_mul(x.b, y.b);
+    Fp6 cross = f6_mul(f6_add(x.a, x.b), f6_add(y.a, y.b));
+    return Fp12{f6_add(aa, f6_mul_v(bb)), f6_sub(f6_sub(cross, aa), bb)};
+}
+Fp12 f12_sqr(const Fp12& x) {  // (a + bw)^2 = (a+b)(a+vb) - ab - v ab + 2ab w
+    Fp6 ab = f6_mul(x.a, x.b);
+    Fp6 t = f6_mul(f6_add(x.a, x.b), f6_add(x.a, f6_mul_v(x.b)));
+    return Fp12{f6_sub(f6_sub(t, ab), f6_mul_v(ab)), f6_add(ab, ab)};
+}
+Fp12 f12_inv(const Fp12& x) {
+    Fp6 t = f6_inv(f6_sub(f6_mul(x.a, x.a), f6_mul_v(f6_mul(x.b, x.b))));
+    return Fp12{f6_mul(x.a, t), f6_neg(f6_mul(x.b, t))};
+}
+
+// x^p: the coefficient c_k of w^k goes to conj(c_k) * gamma^k, gamma = xi^((p-1)/6) = w^(p-1)
+struct FrobTable {
+    Fp2 g[6];
+    FrobTable() {
+        constexpr uint32_t e[12] = {0xfffff1c7u, 0x49aa7fffu, 0x72e35555u, 0x051caaaau, 0xd3c82906u, 0xe688231au,
+                                    0x7deb831fu, 0xe613e1ebu, 0xb5e1f223u, 0x0c849bf3u, 0x5eeaa66fu, 0x045582fcu};  // (p-1)/6
+        Fp2 xi{Fp::one(), Fp::one()}, acc = f2_one();
+        for (int i = 11; i >= 0; i--)
+            for (int bit = 31; bit >= 0; bit--) {
+                acc = f2_sqr(acc);
+                if ((e[i] >> bit) & 1) acc = f2_mul(acc, xi);
+            }
+        g[0] = f2_one();
+        for (int k = 1; k < 6; k++) g[k] = f2_mul(g[k - 1], acc);
+    }
+};
+Fp12 f12_frob(const Fp12& x) {
+    static const FrobTable tab;
+    Fp12 r;
+    for (int i = 0; i < 3; i++) {
+        r.a.c[i] = f2_mul(f2_conj(x.a.c[i]), tab.g[2 * i]);
+        r.b.c[i] = f2_mul(f2_conj(x.b.c[i]), tab.g[2 * i + 1]);
+    }
+    return r;
+}
+
+constexpr uint64_t kAbsX = 0xd201000000010000ull;  // the BLS parameter is -kAbsX
+
+// Untwisting (x', y') -> (x'/w^2, y'/w^3), the line through T with twist slope lam
+// evaluated at P = (xp, yp), times w^3 (in Fp4, erased by the final exponentiation):
+//     (lam xT - yT) - lam xp w^2 + yp w^3
+Fp12 line_value(const Fp2& lam, const G2Aff& t, const Fp& xp, const Fp& yp) {
+    Fp12 l{f6_zero(), f6_zero()};
+    l.a.c[0] = f2_sub(f2_mul(lam, t.x), t.y);
+    l.a.c[1] = f2_neg(f2_mul_fp(lam, xp));
+    l.b.c[1] = Fp2{yp, Fp::zero()};
+    return l;
+}
+
+struct PairIn {
+    Fp xp, yp;
+    G2Aff q;
+};
+
+// prod_i f_{x,Q_i}(P_i); pairs with an identity on either side are dropped before the call
+Fp12 miller_loop(const std::vector<PairIn>& in) {
+    Fp12 f = f12_one();
+    std::vector<G2Aff> t(in.size());
+    for (size_t i = 0; i < in.size(); i++) t[i] = in[i].q;
+    for (int bit = 62; bit >= 0; bit--) {
+        f = f12_sqr(f);
+        for (size_t i = 0; i < in.size(); i++) {
+            Fp2 xx = f2_sqr(t[i].x);
+            Fp2 lam = f2_mul(f2_add(f2_dbl(xx), xx), f2_inv(f2_dbl(t[i].y)));
+            f = f12_mul(f, line_value(lam, t[i], in[i].xp, in[i].yp));
+            Fp2 x3 = f2_sub(f2_sqr(lam), f2_dbl(t[i].x));
+            t[i].y = f2_sub(f2_mul(lam, f2_sub(t[i].x, x3)), t[i].y);
+            t[i].x = x3;
+        }
+        if ((kAbsX >> bit) & 1)
+            for (size_t i = 0; i < in.size(); i++) {
+                const G2Aff& q = in[i].q;
+                Fp2 lam = f2_mul(f2_sub(q.y, t[i].y), f2_inv(f2_sub(q.x, t[i].x)));
+                f = f12_mul(f, line_value(lam, t[i], in[i].xp, in[i].yp));
+                Fp2 x3 = f2_sub(f2_sub(f2_sqr(lam), t[i].x), q.x);
+                t[i].y = f2_sub(f2_mul(lam, f2_sub(t[i].x, x3)), t[i].y);
+                t[i].x = x3;
+            }
+    }
+    return f12_conj(f);  // negative parameter
+}
+
+// g^x for g in the cyclotomic subgroup (inverse = conjugate)
+Fp12 cyc_exp_x(const Fp12& g) {
+    Fp12 r = g;
+    for (int bit = 62; bit >= 0; bit--) {
+        r = f12_sqr(r);
+        if ((kAbsX >> bit) & 1) r = f12_mul(r, g);
+    }
+    return f12_conj(r);
+}
+Fp12 cyc_exp_xm1(const Fp12& g) { return f12_mul(cyc_exp_x(g), f12_conj(g)); }
+
+// f^(3 (p^12-1)/r): easy part (p^6-1)(p^2+1), then 3(p^4-p^2+1)/r = (x-1)^2 (x+p)(x^2+p^2-1) + 3.
+// The factor 3 is coprime to r, so "== 1" is unchanged (blst_fp12_is_one, piano.rs:386, 462).
+Fp12 final_exp3(const Fp12& f) {
+    Fp12 e = f12_mul(f12_conj(f), f12_inv(f));
+    e = f12_mul(f12_frob(f12_frob(e)), e);
+    Fp12 a = cyc_exp_xm1(cyc_exp_xm1(e));
+    Fp12 b = f12_mul(cyc_exp_x(a), f12_frob(a));
+    Fp12 c = f12_mul(f12_mul(cyc_exp_x(cyc_exp_x(b)), f12_frob(f12_frob(b))), f12_conj(b));
+    return f12_mul(c, f12_mul(f12_sqr(e), e));
+}
+
+bool g2_parse(const uint8_t* in, size_t len, G2Aff* out) {
+    if (len == 96) return g2_decompress(in, out);
+    if (len == 192) return g2_deserialize(in, out);
+    return false;
+}
+
+bool gather_pairs(const G1Affine* g1, const uint8_t* g2_192, size_t n, std::vector<PairIn>& out) {
+    for (size_t k = 0; k < n; k++) {
+        G2Aff q;
+        if (!g2_deserialize(g2_192 + 192 * k, &q)) return false;
+        if (q.inf || (g1[k].x.is_zero() && g1[k].y.is_zero())) continue;  // e(O, Q) = e(P, O) = 1
+        out.push_back(PairIn{g1[k].x, g1[k].y, q});
+    }
+    return true;
+}
+
 }  // namespace
 
 bool g2_generate_host(const uint8_t sx[32], const uint8_t sy[32], std::vector<uint8_t> out[3]) {
@@ -290,6 +522,67 @@ bool g2_recode_host(const std::vector<uint8_t>& in, bool to_compressed, std::vec
         if (in.size() != 96 || !g2_decompress(in.data(), &p)) return false;
         out.resize(192);
         g2_serialize(p, out.data());
+    }
+    return true;
+}
+
+// blst_p1_deserialize layout (96 bytes, x || y big-endian, bit 6 of byte 0 = infinity) -> Montgomery affine
+bool g1_deserialize_host(const uint8_t in[96], G1Affine* out) {
+    if (in[0] & 0x80) return false;
+    if (in[0] & 0x40) {
+        out->x = out->y = Fp::zero();
+        return true;
+    }
+    Fp x, y;
+    if (!fp_read(in, 0xff, &x) || !fp_read(in + 48, 0xff, &y)) return false;
+    Fp four = fe_dbl<F>(fe_dbl<F>(Fp::one()));
+    if (fmul(y, y) != fe_add<F>(fmul(fmul(x, x), x), four)) return false;
+    out->x = x;
+    out->y = y;
+    return true;
+}
+
+// out192 = base - k * g2  (g2^tauX - alpha * g2, piano.rs:344-347, 403-410); inputs in
+// either setup-file encoding (96 compressed / 192 serialized), k canonical limbs
+bool g2_sub_mul_host(const std::vector<uint8_t>& base, const std::vector<uint8_t>& g2, const uint32_t k[8], uint8_t out192[192]) {
+    G2Aff b, g;
+    if (!g2_parse(base.data(), base.size(), &b) || !g2_parse(g2.data(), g2.size(), &g)) return false;
+    G2Aff kg = g2_mul(g, k);
+    kg.y = f2_neg(kg.y);
+    G2Jac acc = b.inf ? G2Jac{f2_zero(), f2_one(), f2_zero()} : G2Jac{b.x, b.y, f2_one()};
+    g2_serialize(j_to_affine(j_add_affine(acc, kg)), out192);
+    return true;
+}
+
+bool g2_to_serialized_host(const std::vector<uint8_t>& in, uint8_t out192[192]) {
+    G2Aff p;
+    if (!g2_parse(in.data(), in.size(), &p)) return false;
+    g2_serialize(p, out192);
+    return true;
+}
+
+// prod_k e(g1[k], g2[k]) == 1 ?  1 / 0, or -1 when a G2 element does not parse
+// (pairings_verify_single / pairings_verify, piano.rs:358-388, 422-464)
+int pairing_product_is_one_host(const G1Affine* g1, const uint8_t* g2_192, size_t n) {
+    std::vector<PairIn> pairs;
+    if (!gather_pairs(g1, g2_192, n, pairs)) return -1;
+    if (pairs.empty()) return 1;
+    return f12_is_one(final_exp3(miller_loop(pairs))) ? 1 : 0;
+}
+
+// The value the check above compares with one: (prod_k e(g1[k], g2[k]))^3, written as
+// the 12 Fp coefficients (48-byte big-endian each) of w^0..w^5, real part first.
+bool pairing_value_host(const G1Affine* g1, const uint8_t* g2_192, size_t n, uint8_t out576[576]) {
+    std::vector<PairIn> pairs;
+    if (!gather_pairs(g1, g2_192, n, pairs)) return false;
+    Fp12 v = pairs.empty() ? f12_one() : final_exp3(miller_loop(pairs));
+    for (int i = 0; i < 3; i++) {
+        const Fp2* c[2] = {&v.a.c[i], &v.b.c[i]};
+        for (int h = 0; h < 2; h++) {
+            uint8_t* o = out576 + (size_t)(2 * i + h) * 96;
+            fp_to_be48(fe_from_mont<F>(c[h]->a), o);
+            fp_to_be48(fe_from_mont<F>(c[h]->b), o + 48);
+        }
     }
     return true;
 }

@@ -259,6 +259,28 @@ class PianoBackend:
                                            C.addressof(z), C.addressof(p0), C.addressof(p1)))
         return z.raw, (p0.raw, p1.raw)
 
+    # -- verification ---------------------------------------------------------------------
+    def worker_verify(self, i: int, commitment: bytes, alpha, y, pi: bytes) -> bool:
+        """piano.rs:309-356: e(C - y g^{R_i(tau_Y)}, g2) == e(pi, g2^{tau_X - alpha})."""
+        cb, _ = pack_points([commitment])
+        pb, _ = pack_points([pi])
+        a, yb = pack_scalar(alpha), pack_scalar(y)
+        ok = C.c_int(0)
+        self._chk(self._lib.fb_worker_verify(self._ctx, i, _lib.addr(cb), _lib.addr(a), _lib.addr(yb), _lib.addr(pb),
+                                             C.byref(ok)))
+        return bool(ok.value)
+
+    def master_verify(self, commitment: bytes, beta, alpha, z, pi_f: Tuple[bytes, bytes]) -> bool:
+        """piano.rs:393-420: e(C - z g, g2) == e(pi_0, g2^{tau_X - alpha}) e(pi_1, g2^{tau_Y - beta})."""
+        cb, _ = pack_points([commitment])
+        p0, _ = pack_points([pi_f[0]])
+        p1, _ = pack_points([pi_f[1]])
+        b, a, zb = pack_scalar(beta), pack_scalar(alpha), pack_scalar(z)
+        ok = C.c_int(0)
+        self._chk(self._lib.fb_master_verify(self._ctx, _lib.addr(cb), _lib.addr(b), _lib.addr(a), _lib.addr(zb),
+                                             _lib.addr(p0), _lib.addr(p1), C.byref(ok)))
+        return bool(ok.value)
+
     # -- field-side RPC helpers -------------------------------------------------------
     def fft(self, data: ScalarVec, inverse: bool = False, left: bool = True) -> bytes:
         """fft_left / fft_right (piano.rs:1096-1103) as served by the `fft` RPC."""
@@ -344,3 +366,30 @@ class PianoBackend:
     def dev_worker_open(self, i: int, d_coeffs, count: int, d_alpha, d_out80):
         self._chk(self._lib.fb_dev_worker_open(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_alpha),
                                                _lib.addr(d_out80)))
+
+
+def pairing_check(g1_points96, g2_points192) -> bool:
+    """prod_k e(g1[k], g2[k]) == 1 on serialized points (pairings_verify, piano.rs:422-464).
+    Host arithmetic inside the library: needs neither a context nor a GPU."""
+    lib = _lib.load()
+    g1, g2 = b"".join(g1_points96), b"".join(g2_points192)
+    n = len(g1) // 96
+    if len(g1) != 96 * n or len(g2) != 192 * n:
+        raise FourierError(2, "expected n x 96 bytes of G1 and n x 192 bytes of G2")
+    ok = C.c_int(0)
+    rc = lib.fb_pairing_check(_lib.addr(g1), _lib.addr(g2), n, C.byref(ok))
+    if rc:
+        raise FourierError(rc, "malformed point")
+    return bool(ok.value)
+
+
+def pairing_value(g1_points96, g2_points192) -> bytes:
+    """(prod_k e(g1[k], g2[k]))^3 as 12 big-endian Fp coefficients (see fb_pairing_value)."""
+    lib = _lib.load()
+    g1, g2 = b"".join(g1_points96), b"".join(g2_points192)
+    n = len(g1) // 96
+    out = C.create_string_buffer(576)
+    rc = lib.fb_pairing_value(_lib.addr(g1), _lib.addr(g2), n, C.addressof(out))
+    if rc:
+        raise FourierError(rc, "malformed point")
+    return out.raw

@@ -111,6 +111,26 @@ int fb_master_commit(fb_ctx* ctx, const uint8_t* commitments48, uint64_t count, 
 int fb_master_open(fb_ctx* ctx, const uint8_t* evals_be, const uint8_t* proofs48, uint64_t count,
                    const uint8_t beta_be[32], uint8_t out_z_be[32], uint8_t out_pi0_48[48], uint8_t out_pi1_48[48]);
 
+/* ---- verification -----------------------------------------------------------------
+ * replaces PianoBackend::worker_verify (piano.rs:309-356):
+ *   e(C - y * g^{R_i(tau_Y)}, g2) == e(pi, g2^{tau_X} - alpha * g2)
+ * The G1 side runs on the GPU, the pairing product (pairings_verify_single,
+ * piano.rs:358-388) on the host.  *out_valid = 1 / 0; a malformed input is an error
+ * (the reference rejects it while parsing the request, rpc.rs:330-331). */
+int fb_worker_verify(fb_ctx* ctx, uint64_t i, const uint8_t commitment48[48], const uint8_t alpha_be[32],
+                     const uint8_t y_be[32], const uint8_t proof48[48], int* out_valid);
+/* replaces PianoBackend::master_verify (piano.rs:393-420, pairings_verify :422-464):
+ *   e(C - z * g, g2) == e(pi0, g2^{tau_X} - alpha g2) * e(pi1, g2^{tau_Y} - beta g2) */
+int fb_master_verify(fb_ctx* ctx, const uint8_t commitment48[48], const uint8_t beta_be[32], const uint8_t alpha_be[32],
+                     const uint8_t z_be[32], const uint8_t pi0_48[48], const uint8_t pi1_48[48], int* out_valid);
+/* the pairing product by itself, on serialized points (g1: n x 96 bytes as
+ * blst_p1_serialize, g2: n x 192 bytes as blst_p2_serialize); needs no context and
+ * no GPU.  *out_is_one = (prod_k e(g1[k], g2[k]) == 1). */
+int fb_pairing_check(const uint8_t* g1_96, const uint8_t* g2_192, uint64_t n, int* out_is_one);
+/* the compared value, (prod_k e(g1[k], g2[k]))^3 in GT: 12 Fp coefficients, 48-byte
+ * big-endian, of w^0..w^5 (real part first), Fp12 = Fp2[w]/(w^6 - (1+u)). */
+int fb_pairing_value(const uint8_t* g1_96, const uint8_t* g2_192, uint64_t n, uint8_t out576[576]);
+
 /* ---- field-side RPC helpers -----------------------------------------------------
  * replaces PianoFFTSettings::fft_left / fft_right (piano.rs:1096-1103) as exposed
  * by the `fft` RPC (src/rpc.rs:66-70): left != 0 uses the 2^(n-m) domain. */

@@ -219,3 +219,94 @@ def test_device_resident_rows_match_host_api(small):
         assert cs[i * 48:(i + 1) * 48] == b.worker_commit(i, rows[i])
         y, pi = b.worker_open(i, rows[i], alpha)
         assert ys[i * 32:(i + 1) * 32] == y and ps[i * 48:(i + 1) * 48] == pi
+
+
+# ---------------------------------------------------------------- verify (piano.rs:309-465)
+def test_worker_and_master_verify(small):
+    """pianist_test (piano.rs:1604-1722): every worker opening verifies, the master
+    opening verifies, and any altered input is rejected; answers equal the oracle's."""
+    b, o = small
+    rng = random.Random(31)
+    rows = [[rng.randrange(R) for _ in range(o.T)] for _ in range(o.M)]
+    alpha, beta = rng.randrange(R), rng.randrange(R)
+    flat = [x for row in rows for x in row]
+    commits = b.commit_rows(0, o.M, flat)
+    ys, pis = b.open_rows(0, o.M, flat, alpha)
+    ys = [ys[32 * i:32 * i + 32] for i in range(o.M)] if isinstance(ys, (bytes, bytearray)) else list(ys)
+    for i in range(o.M):
+        assert b.worker_verify(i, commits[i], alpha, ys[i], pis[i])
+    i = 2
+    y_int = int.from_bytes(ys[i], "big")
+    assert not b.worker_verify(i, commits[i], alpha, (y_int + 1) % R, pis[i])
+    assert not b.worker_verify(i, commits[i], (alpha + 1) % R, ys[i], pis[i])
+    assert not b.worker_verify(i, commits[i - 1], alpha, ys[i], pis[i])
+    assert not b.worker_verify(i, commits[i], alpha, ys[i], pis[i - 1])
+    assert not b.worker_verify(i - 1, commits[i], alpha, ys[i], pis[i])  # another machine's R_i
+    # the oracle agrees on one accepted and one rejected case
+    oc, opi = bls.g1_decompress(commits[i]), bls.g1_decompress(pis[i])
+    assert o.worker_verify(i, oc, alpha, y_int, opi)
+    assert not o.worker_verify(i, oc, alpha, (y_int + 1) % R, opi)
+
+    com = b.master_commit(commits)
+    z, (pi0, pi1) = b.master_open(ys, pis, beta)
+    z_int = int.from_bytes(z, "big")
+    assert b.master_verify(com, beta, alpha, z, (pi0, pi1))
+    assert not b.master_verify(com, beta, alpha, (z_int + 1) % R, (pi0, pi1))
+    assert not b.master_verify(com, alpha, beta, z, (pi0, pi1))  # alpha and beta swapped
+    assert not b.master_verify(com, beta, alpha, z, (pi1, pi0))
+    assert not b.master_verify(commits[0], beta, alpha, z, (pi0, pi1))
+
+
+def test_verify_degenerate_and_errors(small):
+    from fourier_b200 import FourierError
+    b, o = small
+    ident = bls.g1_compress(bls.G1_INF)
+    # constant row: zero quotient, proof = identity, still a valid opening
+    ones = [1] * o.T
+    c = b.worker_commit(2, ones)
+    y, pi = b.worker_open(2, ones, 123456789)
+    assert pi == ident and b.worker_verify(2, c, 123456789, y, pi)
+    assert not b.worker_verify(2, c, 123456789, 2, pi)
+    # zero polynomial: commitment, value and proof all trivial
+    assert b.worker_verify(0, ident, 5, 0, ident)
+    assert b.master_verify(ident, 7, 5, 0, (ident, ident))
+    assert not b.master_verify(ident, 7, 5, 1, (ident, ident))
+    with pytest.raises(FourierError) as ei:
+        b.worker_verify(0, ident, R, 0, ident)
+    assert "Invalid scalar" in str(ei.value)
+    with pytest.raises(FourierError) as ei:
+        b.worker_verify(0, ident, 1, R, ident)
+    assert "Invalid scalar" in str(ei.value)
+    with pytest.raises(FourierError):
+        b.worker_verify(o.M, ident, 1, 1, ident)
+    with pytest.raises(FourierError):
+        b.worker_verify(0, b"\x00" * 48, 1, 1, ident)  # not a compressed point
+    with pytest.raises(FourierError):
+        b.master_verify(ident, R + 1, 5, 0, (ident, ident))
+
+
+@pytest.mark.parametrize("n,m", [(4, 0), (6, 3)])
+def test_verify_other_shapes_and_loaded_setup(gpu, n, m, tmp_path):
+    """M = 1 (no right NTT) and a setup that came from an uncompressed file
+    (test_save_and_load_setup, piano.rs:1789-1833)."""
+    from fourier_b200 import PianoBackend
+    b0, o = make(n, m)
+    p = str(tmp_path / "setup.bin")
+    b0.save_setup_to_file(p, False)
+    b0.close()
+    b = PianoBackend(n, m)
+    b.load_setup_from_file(p, False)
+    rng = random.Random(n * 10 + m)
+    rows = [[rng.randrange(R) for _ in range(o.T)] for _ in range(o.M)]
+    alpha, beta = rng.randrange(R), rng.randrange(R)
+    commits = [b.worker_commit(i, rows[i]) for i in range(o.M)]
+    opens = [b.worker_open(i, rows[i], alpha) for i in range(o.M)]
+    for i in range(o.M):
+        assert b.worker_verify(i, commits[i], alpha, opens[i][0], opens[i][1])
+    com = b.master_commit(commits)
+    z, pi_f = b.master_open([y for y, _ in opens], [q for _, q in opens], beta)
+    assert b.master_verify(com, beta, alpha, z, pi_f)
+    assert not b.master_verify(com, beta, alpha, (int.from_bytes(z, "big") + 1) % R, pi_f)
+    if o.M > 1:
+        assert not b.worker_verify(0, commits[1], alpha, opens[1][0], opens[1][1])
+    b.close()
