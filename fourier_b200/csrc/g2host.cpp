@@ -39,8 +39,10 @@ Fp fmul(const Fp& a, const Fp& b) {
     memcpy(x, a.v, 48);
     memcpy(y, b.v, 48);
     memcpy(m, mod.v, 48);
+#pragma GCC unroll 6
     for (int i = 0; i < 6; i++) {
         u128 carry = 0;
+#pragma GCC unroll 6
         for (int j = 0; j < 6; j++) {
             u128 s = (u128)x[i] * y[j] + t[j] + carry;
             t[j] = (uint64_t)s;
@@ -51,6 +53,7 @@ Fp fmul(const Fp& a, const Fp& b) {
         t[7] = (uint64_t)(s >> 64);
         uint64_t q = t[0] * ninv;
         carry = ((u128)q * m[0] + t[0]) >> 64;
+#pragma GCC unroll 6
         for (int j = 1; j < 6; j++) {
             s = (u128)q * m[j] + t[j] + carry;
             t[j - 1] = (uint64_t)s;
@@ -82,6 +85,60 @@ Fp fmul(const Fp& a, const Fp& b) {
     return r;
 }
 
+// a + b, a - b, -a mod p on 64-bit limbs (p < 2^381: the sum of two reduced values fits)
+Fp fadd(const Fp& a, const Fp& b) {
+    typedef unsigned __int128 u128;
+    static const Fp mod = Fp::modulus();
+    uint64_t x[6], y[6], m[6], t[6], d[6];
+    memcpy(x, a.v, 48);
+    memcpy(y, b.v, 48);
+    memcpy(m, mod.v, 48);
+    u128 c = 0;
+#pragma GCC unroll 6
+    for (int j = 0; j < 6; j++) {
+        c += (u128)x[j] + y[j];
+        t[j] = (uint64_t)c;
+        c >>= 64;
+    }
+    uint64_t borrow = 0;
+#pragma GCC unroll 6
+    for (int j = 0; j < 6; j++) {
+        u128 e = (u128)t[j] - m[j] - borrow;
+        d[j] = (uint64_t)e;
+        borrow = (uint64_t)(e >> 64) & 1;
+    }
+    Fp r;
+    memcpy(r.v, borrow ? t : d, 48);
+    return r;
+}
+Fp fsub(const Fp& a, const Fp& b) {
+    typedef unsigned __int128 u128;
+    static const Fp mod = Fp::modulus();
+    uint64_t x[6], y[6], m[6], t[6];
+    memcpy(x, a.v, 48);
+    memcpy(y, b.v, 48);
+    memcpy(m, mod.v, 48);
+    uint64_t borrow = 0;
+#pragma GCC unroll 6
+    for (int j = 0; j < 6; j++) {
+        u128 e = (u128)x[j] - y[j] - borrow;
+        t[j] = (uint64_t)e;
+        borrow = (uint64_t)(e >> 64) & 1;
+    }
+    if (borrow) {
+        u128 c = 0;
+        for (int j = 0; j < 6; j++) {
+            c += (u128)t[j] + m[j];
+            t[j] = (uint64_t)c;
+            c >>= 64;
+        }
+    }
+    Fp r;
+    memcpy(r.v, t, 48);
+    return r;
+}
+Fp fneg(const Fp& a) { return a.is_zero() ? a : fsub(Fp::zero(), a); }
+
 struct Fp2 {
     Fp a, b;  // a + b*u
 };
@@ -89,23 +146,23 @@ Fp2 f2_zero() { return Fp2{Fp::zero(), Fp::zero()}; }
 Fp2 f2_one() { return Fp2{Fp::one(), Fp::zero()}; }
 bool f2_is_zero(const Fp2& x) { return x.a.is_zero() && x.b.is_zero(); }
 bool f2_eq(const Fp2& x, const Fp2& y) { return x.a == y.a && x.b == y.b; }
-Fp2 f2_add(const Fp2& x, const Fp2& y) { return Fp2{fe_add<F>(x.a, y.a), fe_add<F>(x.b, y.b)}; }
-Fp2 f2_sub(const Fp2& x, const Fp2& y) { return Fp2{fe_sub<F>(x.a, y.a), fe_sub<F>(x.b, y.b)}; }
-Fp2 f2_neg(const Fp2& x) { return Fp2{fe_neg<F>(x.a), fe_neg<F>(x.b)}; }
+Fp2 f2_add(const Fp2& x, const Fp2& y) { return Fp2{fadd(x.a, y.a), fadd(x.b, y.b)}; }
+Fp2 f2_sub(const Fp2& x, const Fp2& y) { return Fp2{fsub(x.a, y.a), fsub(x.b, y.b)}; }
+Fp2 f2_neg(const Fp2& x) { return Fp2{fneg(x.a), fneg(x.b)}; }
 Fp2 f2_mul(const Fp2& x, const Fp2& y) {
     Fp aa = fmul(x.a, y.a), bb = fmul(x.b, y.b);
-    Fp cross = fmul(fe_add<F>(x.a, x.b), fe_add<F>(y.a, y.b));
-    return Fp2{fe_sub<F>(aa, bb), fe_sub<F>(fe_sub<F>(cross, aa), bb)};
+    Fp cross = fmul(fadd(x.a, x.b), fadd(y.a, y.b));
+    return Fp2{fsub(aa, bb), fsub(fsub(cross, aa), bb)};
 }
 Fp2 f2_sqr(const Fp2& x) {  // (a+b)(a-b) + 2ab u
     Fp ab = fmul(x.a, x.b);
-    return Fp2{fmul(fe_add<F>(x.a, x.b), fe_sub<F>(x.a, x.b)), fe_dbl<F>(ab)};
+    return Fp2{fmul(fadd(x.a, x.b), fsub(x.a, x.b)), fadd(ab, ab)};
 }
 Fp2 f2_dbl(const Fp2& x) { return f2_add(x, x); }
 Fp2 f2_inv(const Fp2& x) {
-    Fp nrm = fe_add<F>(fmul(x.a, x.a), fmul(x.b, x.b));
+    Fp nrm = fadd(fmul(x.a, x.a), fmul(x.b, x.b));
     Fp i = fe_inv_gcd<F>(nrm);
-    return Fp2{fmul(x.a, i), fe_neg<F>(fmul(x.b, i))};
+    return Fp2{fmul(x.a, i), fneg(fmul(x.b, i))};
 }
 Fp fp_sqrt_candidate(const Fp& x) {
     constexpr uint32_t e[12] = {0xffffeaabu, 0xee7fbfffu, 0xac54ffffu, 0x07aaffffu, 0x3dac3d89u, 0xd9cc34a8u,
@@ -342,8 +399,8 @@ struct Fp6 {
 struct Fp12 {
     Fp6 a, b;
 };
-Fp2 f2_conj(const Fp2& x) { return Fp2{x.a, fe_neg<F>(x.b)}; }
-Fp2 f2_mul_xi(const Fp2& x) { return Fp2{fe_sub<F>(x.a, x.b), fe_add<F>(x.a, x.b)}; }  // (a+bu)(1+u)
+Fp2 f2_conj(const Fp2& x) { return Fp2{x.a, fneg(x.b)}; }
+Fp2 f2_mul_xi(const Fp2& x) { return Fp2{fsub(x.a, x.b), fadd(x.a, x.b)}; }  // (a+bu)(1+u)
 Fp2 f2_mul_fp(const Fp2& x, const Fp& s) { return Fp2{fmul(x.a, s), fmul(x.b, s)}; }
 
 Fp6 f6_zero() { return Fp6{{f2_zero(), f2_zero(), f2_zero()}}; }
@@ -418,12 +475,25 @@ constexpr uint64_t kAbsX = 0xd201000000010000ull;  // the BLS parameter is -kAbs
 // Untwisting (x', y') -> (x'/w^2, y'/w^3), the line through T with twist slope lam
 // evaluated at P = (xp, yp), times w^3 (in Fp4, erased by the final exponentiation):
 //     (lam xT - yT) - lam xp w^2 + yp w^3
-Fp12 line_value(const Fp2& lam, const G2Aff& t, const Fp& xp, const Fp& yp) {
-    Fp12 l{f6_zero(), f6_zero()};
-    l.a.c[0] = f2_sub(f2_mul(lam, t.x), t.y);
-    l.a.c[1] = f2_neg(f2_mul_fp(lam, xp));
-    l.b.c[1] = Fp2{yp, Fp::zero()};
-    return l;
+// T is kept in Jacobian coordinates and the line is scaled by the slope's
+// denominator (an Fp2 factor, erased as well), so the loop has no inversion.
+struct Line {
+    Fp2 c0, c2, c3;  // coefficients of w^0, w^2, w^3
+};
+
+// f * (c0 + c2 w^2 + c3 w^3): as Fp6 pairs the line is (c0, c2, 0) + (0, c3, 0) w
+Fp6 f6_mul_by_01(const Fp6& x, const Fp2& b0, const Fp2& b1) {
+    Fp2 v0 = f2_mul(x.c[0], b0), v1 = f2_mul(x.c[1], b1);
+    Fp2 t01 = f2_sub(f2_sub(f2_mul(f2_add(x.c[0], x.c[1]), f2_add(b0, b1)), v0), v1);
+    return Fp6{{f2_add(v0, f2_mul_xi(f2_mul(x.c[2], b1))), t01, f2_add(f2_mul(x.c[2], b0), v1)}};
+}
+Fp6 f6_mul_by_1(const Fp6& x, const Fp2& b1) {
+    return Fp6{{f2_mul_xi(f2_mul(x.c[2], b1)), f2_mul(x.c[0], b1), f2_mul(x.c[1], b1)}};
+}
+Fp12 f12_mul_line(const Fp12& f, const Line& l) {
+    Fp6 aa = f6_mul_by_01(f.a, l.c0, l.c2), bb = f6_mul_by_1(f.b, l.c3);
+    Fp6 cross = f6_mul_by_01(f6_add(f.a, f.b), l.c0, f2_add(l.c2, l.c3));
+    return Fp12{f6_add(aa, f6_mul_v(bb)), f6_sub(f6_sub(cross, aa), bb)};
 }
 
 struct PairIn {
@@ -431,30 +501,54 @@ struct PairIn {
     G2Aff q;
 };
 
-// prod_i f_{x,Q_i}(P_i); pairs with an identity on either side are dropped before the call
+// T <- 2T, returning the tangent at T scaled by 2 Y Z^3:
+//   lam = 3X^2 / (2YZ);  c0 = 3X^3 - 2Y^2,  c2 = -3X^2 Z^2 xp,  c3 = 2YZ^3 yp
+Line double_step(G2Jac& t, const Fp& xp, const Fp& yp) {
+    Fp2 A = f2_sqr(t.x), B = f2_sqr(t.y), C = f2_sqr(B), zz = f2_sqr(t.z);
+    Fp2 D = f2_dbl(f2_sub(f2_sub(f2_sqr(f2_add(t.x, B)), A), C));
+    Fp2 E = f2_add(f2_dbl(A), A);
+    Fp2 z3 = f2_dbl(f2_mul(t.y, t.z));
+    Line l;
+    l.c0 = f2_sub(f2_mul(E, t.x), f2_dbl(B));
+    l.c2 = f2_neg(f2_mul_fp(f2_mul(E, zz), xp));
+    l.c3 = f2_mul_fp(f2_mul(z3, zz), yp);
+    Fp2 x3 = f2_sub(f2_sqr(E), f2_dbl(D));
+    t.y = f2_sub(f2_mul(E, f2_sub(D, x3)), f2_dbl(f2_dbl(f2_dbl(C))));
+    t.x = x3;
+    t.z = z3;
+    return l;
+}
+
+// T <- T + Q (Q affine), returning the chord through Q scaled by Z3 = Z H:
+//   lam = R / (Z H), H = xQ Z^2 - X, R = yQ Z^3 - Y;  c0 = R xQ - Z3 yQ,  c2 = -R xp,  c3 = Z3 yp
+Line add_step(G2Jac& t, const G2Aff& q, const Fp& xp, const Fp& yp) {
+    Fp2 zz = f2_sqr(t.z);
+    Fp2 H = f2_sub(f2_mul(q.x, zz), t.x);
+    Fp2 R = f2_sub(f2_mul(q.y, f2_mul(zz, t.z)), t.y);
+    Fp2 z3 = f2_mul(t.z, H);
+    Line l;
+    l.c0 = f2_sub(f2_mul(R, q.x), f2_mul(z3, q.y));
+    l.c2 = f2_neg(f2_mul_fp(R, xp));
+    l.c3 = f2_mul_fp(z3, yp);
+    Fp2 hh = f2_sqr(H), hhh = f2_mul(H, hh), v = f2_mul(t.x, hh);
+    Fp2 x3 = f2_sub(f2_sub(f2_sqr(R), hhh), f2_dbl(v));
+    t.y = f2_sub(f2_mul(R, f2_sub(v, x3)), f2_mul(t.y, hhh));
+    t.x = x3;
+    t.z = z3;
+    return l;
+}
+
+// prod_i f_{x,Q_i}(P_i); pairs with an identity on either side are dropped before the
+// call.  Q has order r and the loop scalar is far below r, so T never meets +-Q or O.
 Fp12 miller_loop(const std::vector<PairIn>& in) {
     Fp12 f = f12_one();
-    std::vector<G2Aff> t(in.size());
-    for (size_t i = 0; i < in.size(); i++) t[i] = in[i].q;
+    std::vector<G2Jac> t(in.size());
+    for (size_t i = 0; i < in.size(); i++) t[i] = G2Jac{in[i].q.x, in[i].q.y, f2_one()};
     for (int bit = 62; bit >= 0; bit--) {
         f = f12_sqr(f);
-        for (size_t i = 0; i < in.size(); i++) {
-            Fp2 xx = f2_sqr(t[i].x);
-            Fp2 lam = f2_mul(f2_add(f2_dbl(xx), xx), f2_inv(f2_dbl(t[i].y)));
-            f = f12_mul(f, line_value(lam, t[i], in[i].xp, in[i].yp));
-            Fp2 x3 = f2_sub(f2_sqr(lam), f2_dbl(t[i].x));
-            t[i].y = f2_sub(f2_mul(lam, f2_sub(t[i].x, x3)), t[i].y);
-            t[i].x = x3;
-        }
+        for (size_t i = 0; i < in.size(); i++) f = f12_mul_line(f, double_step(t[i], in[i].xp, in[i].yp));
         if ((kAbsX >> bit) & 1)
-            for (size_t i = 0; i < in.size(); i++) {
-                const G2Aff& q = in[i].q;
-                Fp2 lam = f2_mul(f2_sub(q.y, t[i].y), f2_inv(f2_sub(q.x, t[i].x)));
-                f = f12_mul(f, line_value(lam, t[i], in[i].xp, in[i].yp));
-                Fp2 x3 = f2_sub(f2_sub(f2_sqr(lam), t[i].x), q.x);
-                t[i].y = f2_sub(f2_mul(lam, f2_sub(t[i].x, x3)), t[i].y);
-                t[i].x = x3;
-            }
+            for (size_t i = 0; i < in.size(); i++) f = f12_mul_line(f, add_step(t[i], in[i].q, in[i].xp, in[i].yp));
     }
     return f12_conj(f);  // negative parameter
 }
