@@ -7,7 +7,7 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -O2 --expt-relaxed-constexpr -Xptxas -v $(EXTRA_NVFLAGS)
 CSRC      := fourier_b200/csrc
 BUILD     := build
-CU        := ntt poly msm g1ops srs api engine verify
+CU        := ntt poly msm g1ops srs api engine verify evalform
 OBJS      := $(addprefix $(BUILD)/,$(addsuffix .o,$(CU))) $(BUILD)/g2host.o
 HDRS      := $(wildcard $(CSRC)/*.cuh) include/fourier_b200.h
 LIB       := fourier_b200/libfourier_b200.so

@@ -119,6 +119,10 @@ void fr_fill_zero(Fr* d, size_t n, cudaStream_t st);
 // d_q batch*n coefficients.
 void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, DevBuf& scratch, cudaStream_t st,
                      size_t batch = 1);
+// evalform.cu: y[b] = p_b(alpha) and q_hat[b][j] = ((p_b - y_b)/(X - alpha))(w^j) straight from the
+// evaluations evals[b][j] = p_b(w^j), n = 2^tab.log_n, any alpha (domain points included)
+void evalform_open(const NttTables& tab, const Fr* d_evals, size_t n, size_t batch, const Fr* d_alpha, Fr* d_y, Fr* d_qhat,
+                   DevBuf& scratch, cudaStream_t st);
 
 // ---------------------------------------------------------------- MSM (msm.cu)
 // Window-table entries are padded to one 128-byte line (x in the first 64-byte DRAM atom):

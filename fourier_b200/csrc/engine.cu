@@ -107,6 +107,18 @@ void row_msm(fb_ctx* c, uint64_t i, const Fr* d_scalars, size_t len, G1Xyzz* d_o
 // batch x len) -> y (d_y[batch]) and q_hat = NTT(q || 0) per row in c->fr_b.  Returns q_hat.
 Fr* open_scalars(fb_ctx* c, const NttTables& tab, const Fr* d_coeffs, size_t len, const Fr* d_alpha, Fr* d_y,
                  size_t batch = 1) {
+    // Default: evaluation form, no transform (evalform.cu; same field elements).  FB_OPEN_NTT=1 keeps
+    // the reference's literal sequence iNTT -> eval -> divide -> NTT (piano.rs:193-236).
+    static int literal = -1;
+    if (literal < 0) {
+        const char* e = getenv("FB_OPEN_NTT");
+        literal = e ? atoi(e) : 0;
+    }
+    if (!literal && len >= 2) {
+        Fr* d_q = c->fr_b.as<Fr>(len * batch);
+        evalform_open(tab, d_coeffs, len, batch, d_alpha, d_y, d_q, c->scan, c->stream);
+        return d_q;
+    }
     Fr* d_poly = c->fr_b.as<Fr>(len * batch);
     Fr* d_tmp = c->fr_c.as<Fr>(len * batch);
     ntt_run(tab, c->tile_tw, d_coeffs, d_poly, d_tmp, true, c->stream, batch);          // piano.rs:194

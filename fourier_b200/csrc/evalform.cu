@@ -1,0 +1,221 @@
+// evalform.cu - the field half of worker_open without transforms.
+//
+// The reference (src/engine/piano.rs:193-236) takes the evaluations c_j = p(w^j),
+// interpolates (iNTT), evaluates y = p(alpha), divides q = (p - y)/(X - alpha) and
+// transforms back: q_hat_j = q(w^j).  The same field elements follow directly from
+// the evaluations:
+//     alpha outside the domain:  y = (alpha^N - 1)/N * sum_j c_j w^j / (alpha - w^j)
+//                                q_hat_j = (c_j - y) / (w^j - alpha)
+//     alpha = w^k:               y = c_k,  q_hat_j as above for j != k, and
+//                                q_hat_k = sum_{j != k} (c_j - c_k) w^j / (w^k (w^k - w^j))
+// (exact arithmetic in Fr, so the bytes are identical).  With inv_j = 1/(w^j - alpha)
+// (inv_k = 0), h_j = w^j inv_j, S1 = sum_j c_j h_j and S0 = sum_j h_j:
+//     y = -(alpha^N - 1)/N * S1            or c_k
+//     q_hat_k = -w^(-k) (S1 - c_k S0)
+// inv and h depend on alpha only, so a batch of rows opened at the same alpha (the
+// bivariate row loop) shares them: 2 multiplies per coefficient and row instead of two
+// transforms and a scan.  One binary-GCD inversion per warp (Montgomery's trick).
+#include "common.cuh"
+
+namespace fb {
+
+namespace {
+
+using F = FrParams;
+constexpr int kPer = 4;          // elements per thread in the inversion kernel
+constexpr int kThreads = 128;
+constexpr int kDotPer = 8;       // elements per thread in the dot-product kernel
+constexpr uint32_t kNoIndex = 0xffffffffu;
+
+struct EfArgs {
+    const Fr* lo;     // w^e = hi[e >> lo_bits] * lo[e & mask]
+    const Fr* hi;
+    int lo_bits;
+    int log_n;
+    const Fr* inv_n;  // 1/N
+    const Fr* alpha;
+    const Fr* evals;  // [batch][N]
+    size_t n, batch;
+    Fr* inv;          // [N]
+    Fr* h;            // [N]
+    Fr* partial;      // [batch + 1][nblk]
+    Fr* sums;         // [batch + 1]: S1 per row, then S0
+    Fr* neg_s;        // -(alpha^N - 1)/N
+    uint32_t* kidx;   // index of alpha in the domain, or kNoIndex
+    uint32_t nblk;    // dot-product blocks per row
+    Fr* y;            // [batch]
+    Fr* qhat;         // [batch][N]
+};
+
+__device__ __forceinline__ Fr omega_pow(const EfArgs& a, size_t e) {
+    return fe_mul<F>(a.hi[e >> a.lo_bits], a.lo[e & (((size_t)1 << a.lo_bits) - 1)]);
+}
+
+__device__ __forceinline__ Fr shfl_fr(const Fr& v, int src) {
+    Fr r;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = __shfl_sync(0xffffffffu, v.v[i], src);
+    return r;
+}
+
+// every lane passes a non-zero t and gets 1/t; one inversion per warp
+__device__ __forceinline__ Fr warp_inverse(const Fr& t) {
+    const int lane = threadIdx.x & 31;
+    Fr pre = t, suf = t;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Fr up = shfl_fr(pre, lane - d < 0 ? lane : lane - d);
+        Fr dn = shfl_fr(suf, lane + d > 31 ? lane : lane + d);
+        if (lane >= d) pre = fe_mul<F>(pre, up);
+        if (lane + d <= 31) suf = fe_mul<F>(suf, dn);
+    }
+    Fr inv_total = Fr::zero();
+    if (lane == 31) inv_total = fe_inv_gcd<F>(pre);
+    inv_total = shfl_fr(inv_total, 31);
+    Fr ex_pre = shfl_fr(pre, lane == 0 ? 0 : lane - 1);
+    Fr ex_suf = shfl_fr(suf, lane == 31 ? 31 : lane + 1);
+    Fr r = inv_total;
+    if (lane > 0) r = fe_mul<F>(r, ex_pre);
+    if (lane < 31) r = fe_mul<F>(r, ex_suf);
+    return r;
+}
+
+__global__ void k_ef_consts(EfArgs a) {
+    Fr p = *a.alpha;
+    for (int i = 0; i < a.log_n; i++) p = fe_sqr<F>(p);
+    Fr s = fe_mul<F>(fe_sub<F>(p, Fr::one()), *a.inv_n);
+    *a.neg_s = fe_neg<F>(s);
+    *a.kidx = kNoIndex;
+}
+
+// inv_j = 1/(w^j - alpha) (0 where w^j = alpha, whose index goes to kidx) and h_j = w^j inv_j.
+// Thread t of a block owns elements base + i*kThreads + t, so a warp touches contiguous runs.
+__global__ void __launch_bounds__(kThreads) k_ef_inverse(EfArgs a) {
+    const size_t base = (size_t)blockIdx.x * (kThreads * kPer) + threadIdx.x;
+    const Fr alpha = *a.alpha;
+    Fr w[kPer], pre[kPer];
+    bool zero[kPer];
+    Fr run = Fr::one();
+#pragma unroll
+    for (int i = 0; i < kPer; i++) {
+        const size_t j = base + (size_t)i * kThreads;
+        zero[i] = true;
+        w[i] = Fr::one();
+        if (j < a.n) {
+            w[i] = omega_pow(a, j);
+            Fr d = fe_sub<F>(w[i], alpha);
+            if (d.is_zero()) *a.kidx = (uint32_t)j;
+            else {
+                zero[i] = false;
+                pre[i] = run;  // product of the thread's earlier denominators
+                run = fe_mul<F>(run, d);
+            }
+        }
+    }
+    Fr inv = warp_inverse(run);  // 1 / (product of all the thread's denominators)
+#pragma unroll
+    for (int i = kPer - 1; i >= 0; i--) {
+        const size_t j = base + (size_t)i * kThreads;
+        if (j >= a.n) continue;
+        Fr v = Fr::zero();
+        if (!zero[i]) {
+            v = fe_mul<F>(inv, pre[i]);
+            inv = fe_mul<F>(inv, fe_sub<F>(w[i], alpha));
+        }
+        a.inv[j] = v;
+        a.h[j] = fe_mul<F>(w[i], v);
+    }
+}
+
+__device__ __forceinline__ Fr block_sum(Fr acc, Fr* sm) {
+    sm[threadIdx.x] = acc;
+    for (uint32_t s = kThreads / 2; s > 0; s >>= 1) {
+        __syncthreads();
+        if (threadIdx.x < s) sm[threadIdx.x] = fe_add<F>(sm[threadIdx.x], sm[threadIdx.x + s]);
+    }
+    __syncthreads();
+    return sm[0];
+}
+
+// partial[row][blk] = sum over the block's slice of c_row,j * h_j; row == batch: sum of h_j
+__global__ void __launch_bounds__(kThreads) k_ef_dot(EfArgs a) {
+    __shared__ Fr sm[kThreads];
+    const size_t row = blockIdx.y;
+    const Fr* c = row < a.batch ? a.evals + row * a.n : nullptr;
+    const size_t base = (size_t)blockIdx.x * (kThreads * kDotPer) + threadIdx.x;
+    Fr acc = Fr::zero();
+#pragma unroll
+    for (int i = 0; i < kDotPer; i++) {
+        const size_t j = base + (size_t)i * kThreads;
+        if (j < a.n) acc = fe_add<F>(acc, c ? fe_mul<F>(c[j], a.h[j]) : a.h[j]);
+    }
+    Fr total = block_sum(acc, sm);
+    if (threadIdx.x == 0) a.partial[row * a.nblk + blockIdx.x] = total;
+}
+
+// sums[row] and, for the rows proper, y
+__global__ void __launch_bounds__(kThreads) k_ef_finish(EfArgs a) {
+    __shared__ Fr sm[kThreads];
+    const size_t row = blockIdx.x;
+    Fr acc = Fr::zero();
+    for (uint32_t b = threadIdx.x; b < a.nblk; b += kThreads) acc = fe_add<F>(acc, a.partial[row * a.nblk + b]);
+    Fr total = block_sum(acc, sm);
+    if (threadIdx.x == 0) {
+        a.sums[row] = total;
+        if (row < a.batch) {
+            const uint32_t k = *a.kidx;
+            a.y[row] = k == kNoIndex ? fe_mul<F>(*a.neg_s, total) : a.evals[row * a.n + k];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_ef_quotient(EfArgs a) {
+    const size_t j = (size_t)blockIdx.x * kThreads + threadIdx.x;
+    const size_t row = blockIdx.y;
+    if (j >= a.n) return;
+    const Fr y = a.y[row];
+    Fr q = fe_mul<F>(fe_sub<F>(a.evals[row * a.n + j], y), a.inv[j]);
+    if (j == *a.kidx) {  // alpha = w^k: q_hat_k = -w^(-k) (S1 - c_k S0)
+        Fr t = fe_sub<F>(a.sums[row], fe_mul<F>(y, a.sums[a.batch]));
+        Fr wk_inv = omega_pow(a, (a.n - j) & (a.n - 1));
+        q = fe_neg<F>(fe_mul<F>(wk_inv, t));
+    }
+    a.qhat[row * a.n + j] = q;
+}
+
+}  // namespace
+
+void evalform_open(const NttTables& tab, const Fr* d_evals, size_t n, size_t batch, const Fr* d_alpha, Fr* d_y, Fr* d_qhat,
+                   DevBuf& scratch, cudaStream_t st) {
+    if (!n || !batch) return;
+    EfArgs a;
+    a.lo = tab.lo[0];
+    a.hi = tab.hi[0];
+    a.lo_bits = tab.lo_bits;
+    a.log_n = tab.log_n;
+    a.inv_n = tab.consts + 2;
+    a.alpha = d_alpha;
+    a.evals = d_evals;
+    a.n = n;
+    a.batch = batch;
+    a.nblk = (uint32_t)((n + kThreads * kDotPer - 1) / (kThreads * kDotPer));
+    const size_t need = 2 * n + (batch + 1) * a.nblk + (batch + 1) + 2;
+    Fr* buf = scratch.as<Fr>(need);
+    a.inv = buf;
+    a.h = buf + n;
+    a.partial = a.h + n;
+    a.sums = a.partial + (batch + 1) * a.nblk;
+    a.neg_s = a.sums + (batch + 1);
+    a.kidx = reinterpret_cast<uint32_t*>(a.neg_s + 1);
+    a.y = d_y;
+    a.qhat = d_qhat;
+    prof_mark("open.evalform", st);
+    (++g_launches, k_ef_consts<<<1, 1, 0, st>>>(a));
+    (++g_launches, k_ef_inverse<<<(unsigned)((n + kThreads * kPer - 1) / (kThreads * kPer)), kThreads, 0, st>>>(a));
+    (++g_launches, k_ef_dot<<<dim3(a.nblk, (unsigned)(batch + 1)), kThreads, 0, st>>>(a));
+    (++g_launches, k_ef_finish<<<(unsigned)(batch + 1), kThreads, 0, st>>>(a));
+    (++g_launches, k_ef_quotient<<<dim3((unsigned)((n + kThreads - 1) / kThreads), (unsigned)batch), kThreads, 0, st>>>(a));
+    FB_CUDA(cudaGetLastError());
+}
+
+}  // namespace fb

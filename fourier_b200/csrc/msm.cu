@@ -345,7 +345,9 @@ __device__ __forceinline__ bool warp_slots(const RoundArgs& a, uint32_t O, WarpS
 // pass 2: it is the latency-bound half (GATHER: two random 128-byte lines per slot).  With
 // GATHER it also parks both points (sign applied; identity when the slot has one input) in
 // `stage`, [step][thread], so that pass 2 streams them instead of gathering them again.
-template <bool GATHER>
+// MODE 0: streamed input (rounds >= 1); 1: gather + park the points for pass 2; 2: gather the
+// x coordinates only (pass 2 gathers the points itself)
+template <int MODE>
 __global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
@@ -355,9 +357,9 @@ __global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
     if (!warp_slots(a, a.off_out[a.nbuckets], ws)) return;
     Fp run = Fp::one();
     for (uint32_t j = 0; j < ws.cnt; j++) {
-        const uint2 d = slot_desc<GATHER>(a, ws.base + 32u * j + lane);
+        const uint2 d = slot_desc<MODE != 0>(a, ws.base + 32u * j + lane);
         Fp den;
-        if (GATHER) {
+        if (MODE == 1) {
             G1Affine p1 = load_point(a.pts, a.stride, d.x);
             G1Affine p2 = d.y != kNone ? load_point(a.pts, a.stride, d.y) : G1Affine::inf();
             (void)pair_kind(p1, p2, true, den);
@@ -374,7 +376,8 @@ __global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
 }
 
 // Pass 2: peel the inverses off backwards and add.
-template <bool STAGED>
+// MODE 0: streamed input; 1: the points parked by pass 1; 2: gather through the slot map
+template <int MODE>
 __global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
@@ -386,12 +389,12 @@ __global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
     for (uint32_t j = ws.cnt; j-- > 0;) {
         const uint32_t o = ws.base + 32u * j + lane;
         G1Affine p1, p2;
-        if (STAGED) {
+        if (MODE == 1) {
             const G1Affine* st = a.stage + ((size_t)j * nt + t) * 2;
             p1 = ldg_affine(st);
             p2 = ldg_affine(st + 1);
         } else {
-            const uint2 d = slot_desc<false>(a, o);
+            const uint2 d = slot_desc<MODE == 2>(a, o);
             p1 = load_point(a.pts, a.stride, d.x);
             p2 = d.y != kNone ? load_point(a.pts, a.stride, d.y) : G1Affine::inf();
         }
@@ -717,7 +720,7 @@ int msm_pick_window(size_t n, bool tabulated) {
     for (int c = 4; c <= 22; c++) {
         const double W = (double)msm_num_windows(c);
         const double buckets = (double)((size_t)1 << (c - 1)) * (tabulated ? 1.0 : W);
-        double cost = (double)n * W * 10.0 + buckets * 60.0;
+        double cost = (double)n * W * 10.0 + buckets * 100.0;  // a bucket costs two full XYZZ additions (measured, profiles/)
         if (!tabulated) cost += 255.0 * 9.0;
         if (cost < best_cost) {
             best_cost = cost;
@@ -779,7 +782,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     if (rounds_env == -2) {
         const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
         rounds_env = e ? atoi(e) : -1;
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2<true>, 128, 0));
+        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2<1>, 128, 0));
         if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
     }
     // Measured on B200 (profiles/): three rounds ahead of the XYZZ kernel are ~8% faster than the
@@ -849,18 +852,32 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         ra.inv = s.inv.as<Fp>(rnt);
         ra.stage = nullptr;
         if (r == 0) {
-            ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
+            // Default: pass 1 reads the x coordinates only (two sectors per point) and pass 2, which is
+            // multiplier-bound, hides a second gather of the full points; FB_MSM_REGATHER=0 parks the
+            // points in pass 1 instead (measured 4% slower at 2^20; L2 prefetches made both slower).
+            static int regather = -1;
+            if (regather < 0) {
+                const char* e = getenv("FB_MSM_REGATHER");
+                regather = e ? atoi(e) : 1;
+            }
             (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
             prof_mark("msm.round_pass1", st);
-            (++fb::g_launches, k_round_pass1<true><<<blocks, 128, 0, st>>>(ra));
-            prof_mark("msm.round_pass2", st);
-            (++fb::g_launches, k_round_pass2<true><<<blocks, 128, 0, st>>>(ra));
+            if (regather) {
+                (++fb::g_launches, k_round_pass1<2><<<blocks, 128, 0, st>>>(ra));
+                prof_mark("msm.round_pass2", st);
+                (++fb::g_launches, k_round_pass2<2><<<blocks, 128, 0, st>>>(ra));
+            } else {
+                ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
+                (++fb::g_launches, k_round_pass1<1><<<blocks, 128, 0, st>>>(ra));
+                prof_mark("msm.round_pass2", st);
+                (++fb::g_launches, k_round_pass2<1><<<blocks, 128, 0, st>>>(ra));
+            }
         } else {
             (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
             prof_mark("msm.round_pass1", st);
-            (++fb::g_launches, k_round_pass1<false><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass1<0><<<blocks, 128, 0, st>>>(ra));
             prof_mark("msm.round_pass2", st);
-            (++fb::g_launches, k_round_pass2<false><<<blocks, 128, 0, st>>>(ra));
+            (++fb::g_launches, k_round_pass2<0><<<blocks, 128, 0, st>>>(ra));
         }
         pts_cur = reinterpret_cast<const char*>(ra.out);
         stride_cur = (uint32_t)sizeof(G1Affine);
