@@ -267,23 +267,6 @@ __device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2,
     return 4;
 }
 
-// denominator of a slot from the x coordinates alone; the y coordinates are fetched only
-// when a special case is possible (x == 0 may be the identity (0,0); equal x is a doubling
-// or a cancellation)
-__device__ __forceinline__ Fp slot_den(const char* pts, uint32_t stride, uint2 d) {
-    using F = FpParams;
-    if (d.y == kNone) return Fp::one();
-    Fp x1 = ldg_fp(&point_at(pts, stride, d.x)->x), x2 = ldg_fp(&point_at(pts, stride, d.y)->x);
-    Fp dx = fe_sub<F>(x2, x1);
-    if (x1.is_zero() || x2.is_zero() || dx.is_zero()) {
-        G1Affine p1 = load_point(pts, stride, d.x), p2 = load_point(pts, stride, d.y);
-        Fp den;
-        (void)pair_kind(p1, p2, true, den);
-        return den;
-    }
-    return dx;
-}
-
 __device__ __forceinline__ Fp shfl_fp(const Fp& v, int src) {
     Fp r;
 #pragma unroll
@@ -345,10 +328,37 @@ __device__ __forceinline__ bool warp_slots(const RoundArgs& a, uint32_t O, WarpS
 // pass 2: it is the latency-bound half (GATHER: two random 128-byte lines per slot).  With
 // GATHER it also parks both points (sign applied; identity when the slot has one input) in
 // `stage`, [step][thread], so that pass 2 streams them instead of gathering them again.
+// x coordinates of a slot's two inputs, issued early so that they are in flight while the
+// previous slot's product is formed (a thread's running product is one dependent chain)
+struct SlotX {
+    uint2 d;
+    Fp x1, x2;
+};
+__device__ __forceinline__ void slot_x_load(const char* pts, uint32_t stride, uint2 d, SlotX& s) {
+    s.d = d;
+    if (d.y == kNone) return;
+    s.x1 = ldg_fp(&point_at(pts, stride, d.x)->x);
+    s.x2 = ldg_fp(&point_at(pts, stride, d.y)->x);
+}
+__device__ __forceinline__ Fp slot_x_den(const char* pts, uint32_t stride, const SlotX& s) {
+    using F = FpParams;
+    if (s.d.y == kNone) return Fp::one();
+    Fp dx = fe_sub<F>(s.x2, s.x1);
+    if (s.x1.is_zero() || s.x2.is_zero() || dx.is_zero()) {  // identity, doubling or cancellation: needs y
+        G1Affine p1 = load_point(pts, stride, s.d.x), p2 = load_point(pts, stride, s.d.y);
+        Fp den;
+        (void)pair_kind(p1, p2, true, den);
+        return den;
+    }
+    return dx;
+}
+
 // MODE 0: streamed input (rounds >= 1); 1: gather + park the points for pass 2; 2: gather the
-// x coordinates only (pass 2 gathers the points itself)
+// x coordinates only (pass 2 gathers the points itself).  Launched on pass 2's grid (the running
+// products are per thread), i.e. at 4 CTAs per SM: the loads of the next slot are issued before
+// the current product to keep two slots in flight per thread.
 template <int MODE>
-__global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
+__global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -356,26 +366,32 @@ __global__ void __launch_bounds__(128, 5) k_round_pass1(RoundArgs a) {
     WarpSlots ws;
     if (!warp_slots(a, a.off_out[a.nbuckets], ws)) return;
     Fp run = Fp::one();
-    for (uint32_t j = 0; j < ws.cnt; j++) {
-        const uint2 d = slot_desc<MODE != 0>(a, ws.base + 32u * j + lane);
-        Fp den;
-        if (MODE == 1) {
+    if (MODE == 1) {
+        for (uint32_t j = 0; j < ws.cnt; j++) {
+            const uint2 d = slot_desc<true>(a, ws.base + 32u * j + lane);
+            Fp den;
             G1Affine p1 = load_point(a.pts, a.stride, d.x);
             G1Affine p2 = d.y != kNone ? load_point(a.pts, a.stride, d.y) : G1Affine::inf();
             (void)pair_kind(p1, p2, true, den);
             G1Affine* st = a.stage + ((size_t)j * nt + t) * 2;
             st_affine(st, p1);
             st_affine(st + 1, p2);
-        } else {
-            den = slot_den(a.pts, a.stride, d);
+            run = fe_mul<F>(run, den);
+            a.pref[(size_t)j * nt + t] = run;
         }
-        run = fe_mul<F>(run, den);
-        a.pref[(size_t)j * nt + t] = run;
+    } else {
+        SlotX nxt;
+        if (ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + lane), nxt);
+        for (uint32_t j = 0; j < ws.cnt; j++) {
+            const SlotX cur = nxt;
+            if (j + 1 < ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + 32u * (j + 1) + lane), nxt);
+            run = fe_mul<F>(run, slot_x_den(a.pts, a.stride, cur));
+            a.pref[(size_t)j * nt + t] = run;
+        }
     }
     a.inv[t] = warp_batch_inverse(run);
 }
 
-// Pass 2: peel the inverses off backwards and add.
 // MODE 0: streamed input; 1: the points parked by pass 1; 2: gather through the slot map
 template <int MODE>
 __global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {

@@ -310,3 +310,39 @@ def test_verify_other_shapes_and_loaded_setup(gpu, n, m, tmp_path):
     if o.M > 1:
         assert not b.worker_verify(0, commits[1], alpha, opens[1][0], opens[1][1])
     b.close()
+
+
+# ---------------------------------------------------------------- evaluation-form opening (evalform.cu)
+def test_open_alpha_at_every_domain_point(small):
+    """The transform-free opening has a separate formula when alpha = w^k: every k,
+    single rows and the batched row loop, against the oracle's literal
+    iNTT / eval / divide / NTT sequence (piano.rs:193-236)."""
+    b, o = small
+    rng = random.Random(77)
+    w = bls.root_of_unity(o.t)
+    rows = [[rng.randrange(R) for _ in range(o.T)] for _ in range(o.M)]
+    flat = [x for row in rows for x in row]
+    for k in range(o.T):
+        alpha = pow(w, k, R)
+        y, pi = b.worker_open(1, rows[1], alpha)
+        oy, opi = o.worker_open(1, rows[1], alpha)
+        assert oy == rows[1][k]
+        assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi), k
+    alpha = pow(w, 5, R)
+    ys, pis = b.open_rows(0, o.M, flat, alpha)
+    for i in range(o.M):
+        oy, opi = o.worker_open(i, rows[i], alpha)
+        assert ys[i] == oy.to_bytes(32, "big") and pis[i] == bls.g1_compress(opi)
+
+
+@pytest.mark.parametrize("length", [1, 2, 4])
+def test_open_short_rows(small, length):
+    """Fewer evaluations than columns (a smaller domain), alpha inside and outside it."""
+    b, o = small
+    rng = random.Random(length)
+    coeffs = [rng.randrange(R) for _ in range(length)]
+    lg = length.bit_length() - 1
+    for alpha in (rng.randrange(R), pow(bls.root_of_unity(lg), length - 1, R) if lg else 1):
+        y, pi = b.worker_open(0, coeffs, alpha)
+        oy, opi = o.worker_open(0, coeffs, alpha)
+        assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
