@@ -100,15 +100,32 @@ def run_ntt(args):
         be.dev_ntt(out, tmp, n, True)
         torch.cuda.synchronize()
         ok = bool(torch.equal(tmp, bufs[0]))
-        mul_per_elem = lg / 2 + (2 if lg > 10 else 0) + (2 if lg > 20 else 0)  # butterflies + inter-pass twiddles
+        # SURVEY 8(d)'s fixed accounting: log2(N)/2 Fr multiplies of 136 wide MADs per element (butterflies only; the
+        # inter-pass twiddles are overhead, not credited)
+        mad_per_elem = lg / 2 * 136
         sweep["2^%d" % lg] = {
             "fwd_ms": res["forward"], "inv_ms": res["inverse"],
             "gelem_per_s": world * n / (res["forward"] * 1e-3) / 1e9,
             "hbm_gbs": n * 64 / (res["forward"] * 1e-3) / 1e9, "hbm_frac": n * 64 / (res["forward"] * 1e-3) / 1e9 / peaks["hbm_gbs"],
-            "int_frac": n * mul_per_elem * 128 / (res["forward"] * 1e-3) / int_peak,
+            "int_frac": n * mad_per_elem / (res["forward"] * 1e-3) / int_peak,
             "roundtrip_identity": ok, "buffers": nbuf}
         if lg == 24:
             ms_headline = res["forward"]
+            # e2e: the public host call (fb_ntt) on pinned host buffers: H2D of the 32-byte big-endian scalars, decode,
+            # transform, encode, D2H of the result, all inside the timed region
+            h_in = torch.from_numpy(host.reshape(-1).copy()).pin_memory()
+            h_out = torch.empty(n * 32, dtype=torch.uint8).pin_memory()
+            be.ntt(h_in, False, out=h_out)
+            _barrier(torch, dist, world)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                be.ntt(h_in, False, out=h_out)
+            _barrier(torch, dist, world)
+            ms_e2e = _max_over_ranks(torch, dist, world, dev, [(time.perf_counter() - t0) * 1e3 / args.steps])[0]
+            be.dev_fr_to_be(out, tmp, n)
+            torch.cuda.synchronize()
+            e2e_ok = bool(torch.equal(tmp.cpu(), h_out))
+            del h_in, h_out
         del bufs, out, tmp
     clk = clocks.stop()
     if rank == 0:
@@ -120,12 +137,15 @@ def run_ntt(args):
             "config": {"workload": "Fr NTT sweep 2^16..2^24, natural order in/out (BASELINE config 3)",
                        "parallelism": "1 GPU" if world == 1 else "%d independent replicas (a single NTT does not shard on this path)" % world,
                        "l2": "inputs rotate over >= 256 MB of distinct buffers (larger than L2)"},
-            "e2e": None, "gpu_launches": int(be.launch_count() - total_launches0), "clocks": clk,
+            "e2e": {"value": world * n / (ms_e2e * 1e-3) / 1e9, "unit": "Gelem/s", "h2d_bytes_per_step": n * 32,
+                    "d2h_bytes_per_step": n * 32, "ms": ms_e2e, "matches_device_path": e2e_ok,
+                    "note": "fb_ntt on pinned host buffers; bounded by the two 512 MiB PCIe copies"},
+            "gpu_launches": int(be.launch_count() - total_launches0), "clocks": clk,
             "roofline": {"kernel": "k_ntt_pass (3 passes at 2^24)", "bound": "hbm", "achieved": n * 64 / (ms_headline * 1e-3) / 1e9,
                          "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": n * 64 / (ms_headline * 1e-3) / 1e9 / peaks["hbm_gbs"],
                          "traffic": None, "peak_source": peaks["source"],
                          "note": "algorithmic bytes = 64 B/element (one read + one write); the binding limit is the integer "
-                                 "pipe (log2(N)/2 + 2 per pass boundary Fr multiplies of 128 wide MADs per element): see sweep[*].int_frac "
+                                 "pipe (SURVEY 8d: log2(N)/2 Fr multiplies of 136 wide MADs per element): see sweep[*].int_frac "
                                  "against " + int_src},
             "sweep": sweep,
         }

@@ -87,7 +87,11 @@ struct NttTables {
     Fr* hi[2] = {nullptr, nullptr};   // inverse hi table is pre-scaled by 1/N
     Fr* hi_unscaled_inv = nullptr;    // inverse hi table without the 1/N factor
     Fr* consts = nullptr;             // device: [0] w_N, [1] w_N^-1, [2] 1/N
+    // full[d][j]: single-multiply inter-pass twiddles of pass j, w_N^(y << log_q_j) for y < N >> log_q_j (the inverse
+    // table of pass 0 carries 1/N); nullptr where the table would exceed kNttFullTableLog entries (then hi*lo)
+    Fr* full[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
 };
+constexpr int kNttFullTableLog = 22;
 
 struct NttPlan {
     int npass = 0;

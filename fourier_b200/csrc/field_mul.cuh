@@ -52,6 +52,52 @@ FB_HD Fe<P> fe_mul_portable(const Fe<P>& a, const Fe<P>& b) {
     return r;
 }
 
+// Montgomery step of one CIOS row: adds m*modulus (m = -X[0]/modulus mod 2^32) to the pair of carry chains
+// (Ev aligned at limb 0, Od at limb 1) so that Ev[0] becomes 0.  The caller finishes with Od[N-1] += carry.
+//
+// Fr has modulus = 1 (mod 2^32) and second limb 2^32 - 1, so INV = -1, m = -Ev[0], and the two lowest
+// limb products need no multiplier:  m*1 = m  and  m*(2^32 - 1) = (m - [m != 0]) * 2^32 + Ev[0].
+// That takes 2 of the 16 wide MADs of the row (and the IMAD forming m) off the multiplier pipe.
+template <class P>
+FB_HD void fe_mont_step(uint32_t* Ev, uint32_t* Od) {
+    constexpr int N = P::N;
+    if constexpr (P::INV == 0xffffffffu && P::mod(0) == 1u && P::mod(1) == 0xffffffffu) {
+        const uint32_t e0 = Ev[0];
+        const uint32_t m = 0u - e0;
+        const uint32_t h1 = m - (m != 0u ? 1u : 0u);
+        Od[0] = add_cc(e0, Od[0]);
+        Od[1] = addc_cc(h1, Od[1]);
+#pragma unroll
+        for (int j = 3; j < N; j += 2) {
+            Od[j - 1] = madc_lo_cc(m, P::mod(j), Od[j - 1]);
+            Od[j] = (j == N - 1) ? madc_hi(m, P::mod(j), Od[j]) : madc_hi_cc(m, P::mod(j), Od[j]);
+        }
+        Ev[0] = add_cc(m, e0);
+        Ev[1] = addc_cc(Ev[1], 0u);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            Ev[j] = madc_lo_cc(m, P::mod(j), Ev[j]);
+            Ev[j + 1] = madc_hi_cc(m, P::mod(j), Ev[j + 1]);
+        }
+    } else {
+        const uint32_t m = Ev[0] * P::INV;
+        Od[0] = mad_lo_cc(m, P::mod(1), Od[0]);
+        Od[1] = madc_hi_cc(m, P::mod(1), Od[1]);
+#pragma unroll
+        for (int j = 3; j < N; j += 2) {
+            Od[j - 1] = madc_lo_cc(m, P::mod(j), Od[j - 1]);
+            Od[j] = (j == N - 1) ? madc_hi(m, P::mod(j), Od[j]) : madc_hi_cc(m, P::mod(j), Od[j]);
+        }
+        Ev[0] = mad_lo_cc(m, P::mod(0), Ev[0]);
+        Ev[1] = madc_hi_cc(m, P::mod(0), Ev[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            Ev[j] = madc_lo_cc(m, P::mod(j), Ev[j]);
+            Ev[j + 1] = madc_hi_cc(m, P::mod(j), Ev[j + 1]);
+        }
+    }
+}
+
 // Carry-chain CIOS.  State: two limb arrays E ("even", aligned at limb 0) and O
 // ("odd", aligned at limb 1) with  V = E + O * 2^32.  Products a_j*b_i with even j
 // land on E's aligned limb pairs, odd j on O's, so each row is two carry chains of
@@ -75,21 +121,7 @@ FB_HD Fe<P> fe_mul(const Fe<P>& a, const Fe<P>& b) {
             O[j] = mul_lo(a.v[j + 1], bi);
             O[j + 1] = mul_hi(a.v[j + 1], bi);
         }
-        const uint32_t m = E[0] * P::INV;
-        O[0] = mad_lo_cc(m, P::mod(1), O[0]);
-        O[1] = madc_hi_cc(m, P::mod(1), O[1]);
-#pragma unroll
-        for (int j = 3; j < N; j += 2) {
-            O[j - 1] = madc_lo_cc(m, P::mod(j), O[j - 1]);
-            O[j] = (j == N - 1) ? madc_hi(m, P::mod(j), O[j]) : madc_hi_cc(m, P::mod(j), O[j]);
-        }
-        E[0] = mad_lo_cc(m, P::mod(0), E[0]);
-        E[1] = madc_hi_cc(m, P::mod(0), E[1]);
-#pragma unroll
-        for (int j = 2; j < N; j += 2) {
-            E[j] = madc_lo_cc(m, P::mod(j), E[j]);
-            E[j + 1] = madc_hi_cc(m, P::mod(j), E[j + 1]);
-        }
+        fe_mont_step<P>(E, O);
         O[N - 1] = addc(O[N - 1], 0);
     }
     // ---- rows 1..N-1
@@ -115,21 +147,7 @@ FB_HD Fe<P> fe_mul(const Fe<P>& a, const Fe<P>& b) {
             nE[j + 1] = madc_hi_cc(a.v[j], bi, nE[j + 1]);
         }
         nO[N - 1] = addc(nO[N - 1], 0);
-        const uint32_t m = nE[0] * P::INV;
-        nO[0] = mad_lo_cc(m, P::mod(1), nO[0]);
-        nO[1] = madc_hi_cc(m, P::mod(1), nO[1]);
-#pragma unroll
-        for (int j = 3; j < N; j += 2) {
-            nO[j - 1] = madc_lo_cc(m, P::mod(j), nO[j - 1]);
-            nO[j] = (j == N - 1) ? madc_hi(m, P::mod(j), nO[j]) : madc_hi_cc(m, P::mod(j), nO[j]);
-        }
-        nE[0] = mad_lo_cc(m, P::mod(0), nE[0]);
-        nE[1] = madc_hi_cc(m, P::mod(0), nE[1]);
-#pragma unroll
-        for (int j = 2; j < N; j += 2) {
-            nE[j] = madc_lo_cc(m, P::mod(j), nE[j]);
-            nE[j + 1] = madc_hi_cc(m, P::mod(j), nE[j + 1]);
-        }
+        fe_mont_step<P>(nE, nO);
         nO[N - 1] = addc(nO[N - 1], 0);
         E = nE;
         O = nO;

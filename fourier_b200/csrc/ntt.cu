@@ -84,6 +84,7 @@ struct PassArgs {
     int twiddle, scale;
     const Fr* tw_lo;
     const Fr* tw_hi;
+    const Fr* tw_full;  // single-multiply table of this pass boundary, or nullptr (then tw_hi * tw_lo)
     const Fr* tile_tw;
     const Fr* n_inv;
     unsigned long long batch_stride;  // elements between consecutive transforms of a batch (blockIdx.y)
@@ -111,16 +112,18 @@ __device__ __forceinline__ Fr ldg_fr(const Fr* p) {
 
 // One group of G DIF stages (s_hi .. s_hi-G+1) over the staged tile.  A work item is the set of
 // 2^G rows  base | (m << s_lo)  (m < 2^G; base has zero bits in [s_lo, s_hi]) of one column.
-template <int G>
+// LAST: the group ends at stage 0 (s_lo == 0), where the twiddle exponent depends on m alone, so the
+// butterflies whose twiddle is 1 (all of stage 0, half of stage 1, a quarter of stage 2) are plain add/sub.
+template <int G, bool LAST>
 __device__ __forceinline__ void ntt_group(uint4* s0, uint4* s1, const uint4* t0, const uint4* t1, int s_hi, int log_r, int log_b,
                                           uint32_t tile, uint32_t tid, uint32_t nt) {
     constexpr int M = 1 << G;
-    const int s_lo = s_hi - G + 1;
+    const int s_lo = LAST ? 0 : s_hi - G + 1;
     const uint32_t B = 1u << log_b;
     for (uint32_t q = tid; q < (tile >> G); q += nt) {
         const uint32_t cb = q & (B - 1), qr = q >> log_b;
-        const uint32_t low = qr & ((1u << s_lo) - 1u);
-        const uint32_t base = ((qr >> s_lo) << (s_hi + 1)) | low;
+        const uint32_t low = LAST ? 0u : (qr & ((1u << s_lo) - 1u));
+        const uint32_t base = LAST ? (qr << G) : (((qr >> s_lo) << (s_hi + 1)) | low);
         Fr x[M];
 #pragma unroll
         for (int m = 0; m < M; m++) x[m] = lds_fr(s0, s1, ((base | ((uint32_t)m << s_lo)) << log_b) | cb);
@@ -133,8 +136,11 @@ __device__ __forceinline__ void ntt_group(uint4* s0, uint4* s1, const uint4* t0,
                 Fr u = x[m], v = x[m | (1 << t)];
                 x[m] = fe_add<FrParams>(u, v);
                 Fr dif = fe_sub<FrParams>(u, v);
-                if (st > 0) {
-                    // twiddle w_R^(j * 2^(log_r-1-st)),  j = row index mod 2^st
+                // twiddle w_R^(j * 2^(log_r-1-st)),  j = row index mod 2^st
+                if (LAST) {
+                    const uint32_t j = (uint32_t)(m & ((1 << t) - 1));
+                    if (j != 0) dif = fe_mul<FrParams>(dif, lds_fr(t0, t1, j << (log_r - 1 - st)));
+                } else {
                     const uint32_t j = low | ((uint32_t)(m & ((1 << t) - 1)) << s_lo);
                     dif = fe_mul<FrParams>(dif, lds_fr(t0, t1, j << (log_r - 1 - st)));
                 }
@@ -146,7 +152,10 @@ __device__ __forceinline__ void ntt_group(uint4* s0, uint4* s1, const uint4* t0,
     }
 }
 
-__global__ void __launch_bounds__(256) k_ntt_pass(PassArgs a) {
+// MAXG: stages per register-resident group.  3: 8 elements per thread, 128 registers, 16 warps/SM;
+// 2: 4 elements per thread, 85 registers, 24 warps/SM (one more shared-memory round trip per 6 stages).
+template <int MAXG>
+__global__ void __launch_bounds__(256, MAXG == 3 ? 2 : 3) k_ntt_pass(PassArgs a) {
     extern __shared__ uint4 smem[];
     const uint32_t R = 1u << a.log_r, B = 1u << a.log_b;
     const uint32_t tile = R << a.log_b;
@@ -175,12 +184,29 @@ __global__ void __launch_bounds__(256) k_ntt_pass(PassArgs a) {
     // radix-2 decimation-in-frequency stages (natural in, bit-reversed out), taken in groups of up
     // to 3: a thread pulls the 2^g rows that interact over the group's stages into registers,
     // runs the g stages there and writes them back - one shared-memory round trip and one
-    // barrier per group instead of per stage.
+    // barrier per group instead of per stage.  The short groups come first so that the last group,
+    // the one with the multiplier-free butterflies, is a full one: 10 = 2+2+3+3, 8 = 2+3+3, 7 = 2+2+3.
     for (int s_hi = a.log_r - 1; s_hi >= 0;) {
-        const int g = s_hi >= 2 ? 3 : s_hi + 1;
-        if (g == 3) ntt_group<3>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
-        else if (g == 2) ntt_group<2>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
-        else ntt_group<1>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+        const int left = s_hi + 1;
+        int g;
+        if (MAXG == 3) {
+            if (left <= 3) g = left;
+            else if (left % 3 == 0) g = 3;
+            else if (left % 3 == 2) g = 2;
+            else g = left == 4 ? 1 : 2;  // left % 3 == 1: 2 + 2 + 3k, except 4 = 1 + 3
+        } else {
+            g = (left <= 2) ? left : ((left & 1) ? 1 : 2);  // odd: 1 + 2k
+        }
+        const bool last = (g == left);
+        if (last) {
+            if (MAXG == 3 && g == 3) ntt_group<3, true>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+            else if (g == 2) ntt_group<2, true>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+            else ntt_group<1, true>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+        } else {
+            if (MAXG == 3 && g == 3) ntt_group<3, false>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+            else if (g == 2) ntt_group<2, false>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+            else ntt_group<1, false>(s0, s1, t0, t1, s_hi, a.log_r, a.log_b, tile, tid, nt);
+        }
         __syncthreads();
         s_hi -= g;
     }
@@ -204,9 +230,13 @@ __global__ void __launch_bounds__(256) k_ntt_pass(PassArgs a) {
         unsigned long long c = c0 + cb;
         unsigned long long rest = c >> a.log_q;
         if (a.twiddle) {
-            unsigned long long x = ((unsigned long long)k * rest) << a.log_q;
-            Fr t = fe_mul<FrParams>(ldg_fr(a.tw_hi + (x >> a.lo_bits)), ldg_fr(a.tw_lo + (x & lo_mask)));
-            val = fe_mul<FrParams>(val, t);
+            if (a.tw_full) {
+                val = fe_mul<FrParams>(val, ldg_fr(a.tw_full + (unsigned long long)k * rest));
+            } else {
+                unsigned long long x = ((unsigned long long)k * rest) << a.log_q;
+                Fr t = fe_mul<FrParams>(ldg_fr(a.tw_hi + (x >> a.lo_bits)), ldg_fr(a.tw_lo + (x & lo_mask)));
+                val = fe_mul<FrParams>(val, t);
+            }
         }
         if (a.scale) val = fe_mul<FrParams>(val, ninv);
         unsigned long long o = (rest << (a.log_q + a.log_r)) | ((unsigned long long)k << a.log_q) | (c & qmask);
@@ -220,20 +250,30 @@ constexpr int kTileLog = 11;  // elements staged per CTA = 2^11 (64 KiB of share
 
 }  // namespace
 
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
+}
+
+// Tuning knobs (defaults are the measured optimum, profiles/r1_v7_ntt_sweep.txt): largest radix per pass,
+// elements staged per CTA, columns per tile.
+static int ntt_max_log_r() { static int v = env_int("FB_NTT_MAXR", 10); return v < 1 ? 1 : (v > 10 ? 10 : v); }
+static int ntt_tile_log() { static int v = env_int("FB_NTT_TILE", kTileLog); return v < 6 ? 6 : (v > 12 ? 12 : v); }
+static int ntt_group_stages() { static int v = env_int("FB_NTT_G", 3); return v == 2 ? 2 : 3; }
+static int ntt_threads_div() { static int v = env_int("FB_NTT_TDIV", 8); return v < 2 ? 2 : (v > 16 ? 16 : v); }
+static int ntt_max_log_b() { static int v = env_int("FB_NTT_MAXB", 3); return v < 0 ? 0 : v; }
+
 NttPlan ntt_make_plan(int log_n) {
     NttPlan p;
-    if (log_n <= 10) {
-        p.npass = 1;
-        p.log_r[0] = log_n;
-    } else if (log_n <= 20) {
-        p.npass = 2;
-        p.log_r[0] = (log_n + 1) / 2;
-        p.log_r[1] = log_n - p.log_r[0];
-    } else {
-        p.npass = 3;
-        p.log_r[0] = (log_n + 2) / 3;
-        p.log_r[1] = (log_n - p.log_r[0] + 1) / 2;
-        p.log_r[2] = log_n - p.log_r[0] - p.log_r[1];
+    const int maxr = ntt_max_log_r();
+    int np = (log_n + maxr - 1) / maxr;
+    if (np < 1) np = 1;
+    if (np > 4) np = 4;
+    p.npass = np;
+    int left = log_n;
+    for (int j = 0; j < np; j++) {  // as even as possible, larger radices first
+        p.log_r[j] = (left + (np - j) - 1) / (np - j);
+        left -= p.log_r[j];
     }
     return p;
 }
@@ -263,6 +303,21 @@ void ntt_build_tables(NttTables& t, int log_n, cudaStream_t st) {
     FB_CUDA(cudaMalloc(&t.hi_unscaled_inv, nhi * sizeof(Fr)));
     (++fb::g_launches, k_pow_table<<<(nhi + 127) / 128, 128, 0, st>>>(t.hi_unscaled_inv, nhi, consts + 1, t.lo_bits, nullptr));
     t.consts = consts;
+    // single-multiply tables per pass boundary (pass j spans N >> log_q_j exponents)
+    NttPlan plan = ntt_make_plan(log_n);
+    int log_q = 0;
+    for (int j = 0; j + 1 < plan.npass; j++) {
+        const int log_cnt = log_n - log_q;
+        if (log_cnt <= kNttFullTableLog) {
+            const uint32_t cnt = 1u << log_cnt;
+            for (int d = 0; d < 2; d++) {
+                FB_CUDA(cudaMalloc(&t.full[d][j], (size_t)cnt * sizeof(Fr)));
+                (++fb::g_launches, k_pow_table<<<(cnt + 127) / 128, 128, 0, st>>>(t.full[d][j], cnt, consts + d, log_q,
+                                                                                 (d == 1 && j == 0) ? consts + 2 : nullptr));
+            }
+        }
+        log_q += plan.log_r[j];
+    }
     FB_CUDA(cudaGetLastError());
 }
 
@@ -272,6 +327,11 @@ void ntt_free_tables(NttTables& t) {
         if (t.hi[d]) cudaFree(t.hi[d]);
         t.lo[d] = t.hi[d] = nullptr;
     }
+    for (int d = 0; d < 2; d++)
+        for (int j = 0; j < 3; j++) {
+            if (t.full[d][j]) cudaFree(t.full[d][j]);
+            t.full[d][j] = nullptr;
+        }
     if (t.hi_unscaled_inv) cudaFree(t.hi_unscaled_inv);
     if (t.consts) cudaFree(t.consts);
     t.hi_unscaled_inv = nullptr;
@@ -285,7 +345,8 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
     if (batch > 65535) throw CudaError{"ntt: batch too large"};
     static bool attr_set = false;
     if (!attr_set) {
-        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set = true;
     }
     const int log_n = tab.log_n;
@@ -298,9 +359,10 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         a.log_r = plan.log_r[j];
         int log_c = log_n - a.log_r;
         a.C = 1ull << log_c;
-        a.log_b = kTileLog - a.log_r;
+        a.log_b = ntt_tile_log() - a.log_r;
+        if (a.log_b < 0) a.log_b = 0;
         if (a.log_b > log_c) a.log_b = log_c;
-        if (a.log_b > 3) a.log_b = 3;
+        if (a.log_b > ntt_max_log_b()) a.log_b = ntt_max_log_b();
         // enough tiles per SM that the last, partial wave is short (2^20 = 1024 x 1024: 512 tiles of 2 columns
         // leave 4 tiles on some SMs and 3 on others; 1024 tiles of one column balance to 7 vs 6.9)
         while (a.log_b > 0 && ((a.C * batch) >> a.log_b) < 8ull * kNumSMs) a.log_b--;
@@ -312,22 +374,25 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         a.tw_lo = tab.lo[d];
         // the inverse transform's 1/N rides on the first pass's twiddle table
         a.tw_hi = inverse ? (j == 0 ? tab.hi[1] : tab.hi_unscaled_inv) : tab.hi[0];
+        a.tw_full = (j < 3) ? tab.full[d][j] : nullptr;
         a.tile_tw = a.log_r >= 1 ? tt.base[d] + ((1u << (a.log_r - 1)) - 1) : tt.base[d];
         a.n_inv = tab.consts + 2;
         a.in = src;
         Fr* dst;
-        if (plan.npass == 1) dst = out;
-        else if (j == 0) dst = scratch;
-        else dst = out;
+        // the last pass may run in place (a CTA writes exactly the positions it read); the others ping-pong
+        if (last) dst = out;
+        else dst = (j % 2 == 0) ? scratch : out;
         a.out = dst;
         uint32_t tile = 1u << (a.log_r + a.log_b);
-        uint32_t threads = tile / 8 < 32 ? 32 : (tile / 8 > 256 ? 256 : tile / 8);
+        const uint32_t tdiv = (uint32_t)ntt_threads_div();
+        uint32_t threads = tile / tdiv < 32 ? 32 : (tile / tdiv > 256 ? 256 : tile / tdiv);
         size_t smem = (size_t)tile * 32 + ((size_t)1 << a.log_r) * 16;
         unsigned long long blocks = a.C >> a.log_b;
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
         prof_mark(names[j], st);
         a.batch_stride = 1ull << log_n;
-        (++fb::g_launches, k_ntt_pass<<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
+        if (ntt_group_stages() == 3) (++fb::g_launches, k_ntt_pass<3><<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
+        else (++fb::g_launches, k_ntt_pass<2><<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
         src = dst;
         log_q += a.log_r;
     }

@@ -289,11 +289,16 @@ class PianoBackend:
         self._chk(self._lib.fb_fft(self._ctx, int(left), int(inverse), _lib.addr(buf), n, C.addressof(out)))
         return out.raw[: FR_BYTES * n]
 
-    def ntt(self, data: ScalarVec, inverse: bool = False) -> bytes:
+    def ntt(self, data: ScalarVec, inverse: bool = False, out=None):
+        """Natural-order NTT of 32-byte big-endian scalars on host buffers.  `out`: a caller-owned host buffer
+        of 32*n bytes (numpy / torch, e.g. pinned) to receive the result in place of a returned bytes object."""
         buf, n = pack_scalars(data)
-        out = C.create_string_buffer(FR_BYTES * max(n, 1))
-        self._chk(self._lib.fb_ntt(self._ctx, int(inverse), _lib.addr(buf), n, C.addressof(out)))
-        return out.raw[: FR_BYTES * n]
+        if out is not None:
+            self._chk(self._lib.fb_ntt(self._ctx, int(inverse), _lib.addr(buf), n, _lib.addr(out)))
+            return None
+        res = C.create_string_buffer(FR_BYTES * max(n, 1))
+        self._chk(self._lib.fb_ntt(self._ctx, int(inverse), _lib.addr(buf), n, C.addressof(res)))
+        return res.raw[: FR_BYTES * n]
 
     def evaluate(self, poly: ScalarVec, x) -> bytes:
         """FsPoly::eval as served by the `evaluate` RPC (rpc.rs:60-64)."""

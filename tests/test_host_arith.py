@@ -43,6 +43,10 @@ def test_field_ops(L, name, m, n):
     cases = [(0, 0), (1, 1), (m - 1, m - 1), (m - 1, 1), (RR % m, RR % m), (m - 1, 0)]
     cases += [(rng.randrange(m), rng.randrange(m)) for _ in range(2000)]
     cases += [((1 << k) % m, m - 1 - ((1 << j) % m)) for k in range(0, 32 * n, 37) for j in range(0, 32 * n, 53)]
+    # rows whose Montgomery quotient digit is 0 (low limbs of the running sum vanish): the m == 0 branch of
+    # Fr's multiplier-free low limbs (fe_mont_step)
+    cases += [(1 << (32 * i), (1 << (32 * j)) + (rng.randrange(m) >> (32 * k) << (32 * k))) for i in range(n - 1) for j in range(n - 1) for k in (1, 3)]
+    cases = [(a % m, b % m) for a, b in cases]
     r = (ctypes.c_uint32 * n)()
     for a, b in cases:
         e = a * b * Ri % m
