@@ -84,10 +84,6 @@ int fb_ctx_create(uint32_t n, uint32_t m, int device, fb_ctx** out) {
     c->M = (size_t)1 << m;
     try {
         FB_CUDA(cudaSetDevice(device));
-        if (const char* e = getenv("FB_L2_FETCH")) {  // tuning knob: L2 fetch granularity in bytes (32 / 64 / 128)
-            const int g = atoi(e);
-            if (g == 32 || g == 64 || g == 128) FB_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g));
-        }
         FB_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
         c->stream = c->own_stream;
         FB_CUDA(cudaMalloc(&c->d_err, 2 * sizeof(int)));

@@ -91,7 +91,7 @@ struct NttTables {
     // table of pass 0 carries 1/N); nullptr where the table would exceed kNttFullTableLog entries (then hi*lo)
     Fr* full[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
 };
-constexpr int kNttFullTableLog = 22;
+constexpr int kNttFullTableLog = 24;  // 2^24 entries = 512 MiB per direction, built only for sizes that are used
 
 struct NttPlan {
     int npass = 0;

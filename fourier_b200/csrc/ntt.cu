@@ -153,9 +153,10 @@ __device__ __forceinline__ void ntt_group(uint4* s0, uint4* s1, const uint4* t0,
 }
 
 // MAXG: stages per register-resident group.  3: 8 elements per thread, 128 registers, 16 warps/SM;
-// 2: 4 elements per thread, 85 registers, 24 warps/SM (one more shared-memory round trip per 6 stages).
-template <int MAXG>
-__global__ void __launch_bounds__(256, MAXG == 3 ? 2 : 3) k_ntt_pass(PassArgs a) {
+// 2: 4 elements per thread, 80 registers, 24 warps/SM (one more shared-memory round trip per 6 stages).
+// (A 64-register build of the latter, 32 warps/SM, measured no faster: profiles/r1_v7_ntt_sweep.txt.)
+template <int MAXG, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_ntt_pass(PassArgs a) {
     extern __shared__ uint4 smem[];
     const uint32_t R = 1u << a.log_r, B = 1u << a.log_b;
     const uint32_t tile = R << a.log_b;
@@ -256,11 +257,12 @@ static int env_int(const char* name, int dflt) {
 }
 
 // Tuning knobs (defaults are the measured optimum, profiles/r1_v7_ntt_sweep.txt): largest radix per pass,
-// elements staged per CTA, columns per tile.
+// elements staged per CTA, columns per tile, stages per register group, elements per thread.
 static int ntt_max_log_r() { static int v = env_int("FB_NTT_MAXR", 10); return v < 1 ? 1 : (v > 10 ? 10 : v); }
 static int ntt_tile_log() { static int v = env_int("FB_NTT_TILE", kTileLog); return v < 6 ? 6 : (v > 12 ? 12 : v); }
-static int ntt_group_stages() { static int v = env_int("FB_NTT_G", 3); return v == 2 ? 2 : 3; }
-static int ntt_threads_div() { static int v = env_int("FB_NTT_TDIV", 8); return v < 2 ? 2 : (v > 16 ? 16 : v); }
+static int ntt_group_stages() { static int v = env_int("FB_NTT_G", 2); return v == 3 ? 3 : 2; }
+static int ntt_threads_div() { static int v = env_int("FB_NTT_TDIV", 4); return v < 2 ? 2 : (v > 16 ? 16 : v); }
+static int ntt_full_table_log() { static int v = env_int("FB_NTT_FULL", kNttFullTableLog); return v; }
 static int ntt_max_log_b() { static int v = env_int("FB_NTT_MAXB", 3); return v < 0 ? 0 : v; }
 
 NttPlan ntt_make_plan(int log_n) {
@@ -308,7 +310,7 @@ void ntt_build_tables(NttTables& t, int log_n, cudaStream_t st) {
     int log_q = 0;
     for (int j = 0; j + 1 < plan.npass; j++) {
         const int log_cnt = log_n - log_q;
-        if (log_cnt <= kNttFullTableLog) {
+        if (log_cnt <= ntt_full_table_log()) {
             const uint32_t cnt = 1u << log_cnt;
             for (int d = 0; d < 2; d++) {
                 FB_CUDA(cudaMalloc(&t.full[d][j], (size_t)cnt * sizeof(Fr)));
@@ -345,8 +347,8 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
     if (batch > 65535) throw CudaError{"ntt: batch too large"};
     static bool attr_set = false;
     if (!attr_set) {
-        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set = true;
     }
     const int log_n = tab.log_n;
@@ -391,8 +393,9 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
         prof_mark(names[j], st);
         a.batch_stride = 1ull << log_n;
-        if (ntt_group_stages() == 3) (++fb::g_launches, k_ntt_pass<3><<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
-        else (++fb::g_launches, k_ntt_pass<2><<<dim3((unsigned)blocks, (unsigned)batch), threads, smem, st>>>(a));
+        const dim3 grid((unsigned)blocks, (unsigned)batch);
+        if (ntt_group_stages() == 3) (++fb::g_launches, k_ntt_pass<3, 2><<<grid, threads, smem, st>>>(a));
+        else (++fb::g_launches, k_ntt_pass<2, 3><<<grid, threads, smem, st>>>(a));
         src = dst;
         log_q += a.log_r;
     }
