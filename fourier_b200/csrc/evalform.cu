@@ -14,8 +14,9 @@
 //     q_hat_k = -w^(-k) (S1 - c_k S0)
 // inv and h depend on alpha only, so a batch of rows opened at the same alpha (the
 // bivariate row loop) shares them: 2 multiplies per coefficient and row instead of two
-// transforms and a scan.  One binary-GCD inversion per warp (Montgomery's trick).
+// transforms and a scan.  One binary-GCD inversion per CTA (Montgomery's trick, batchinv.cuh).
 #include "common.cuh"
+#include "batchinv.cuh"
 
 namespace fb {
 
@@ -51,35 +52,6 @@ __device__ __forceinline__ Fr omega_pow(const EfArgs& a, size_t e) {
     return fe_mul<F>(a.hi[e >> a.lo_bits], a.lo[e & (((size_t)1 << a.lo_bits) - 1)]);
 }
 
-__device__ __forceinline__ Fr shfl_fr(const Fr& v, int src) {
-    Fr r;
-#pragma unroll
-    for (int i = 0; i < 8; i++) r.v[i] = __shfl_sync(0xffffffffu, v.v[i], src);
-    return r;
-}
-
-// every lane passes a non-zero t and gets 1/t; one inversion per warp
-__device__ __forceinline__ Fr warp_inverse(const Fr& t) {
-    const int lane = threadIdx.x & 31;
-    Fr pre = t, suf = t;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        Fr up = shfl_fr(pre, lane - d < 0 ? lane : lane - d);
-        Fr dn = shfl_fr(suf, lane + d > 31 ? lane : lane + d);
-        if (lane >= d) pre = fe_mul<F>(pre, up);
-        if (lane + d <= 31) suf = fe_mul<F>(suf, dn);
-    }
-    Fr inv_total = Fr::zero();
-    if (lane == 31) inv_total = fe_inv_gcd<F>(pre);
-    inv_total = shfl_fr(inv_total, 31);
-    Fr ex_pre = shfl_fr(pre, lane == 0 ? 0 : lane - 1);
-    Fr ex_suf = shfl_fr(suf, lane == 31 ? 31 : lane + 1);
-    Fr r = inv_total;
-    if (lane > 0) r = fe_mul<F>(r, ex_pre);
-    if (lane < 31) r = fe_mul<F>(r, ex_suf);
-    return r;
-}
-
 __global__ void k_ef_consts(EfArgs a) {
     Fr p = *a.alpha;
     for (int i = 0; i < a.log_n; i++) p = fe_sqr<F>(p);
@@ -112,7 +84,8 @@ __global__ void __launch_bounds__(kThreads) k_ef_inverse(EfArgs a) {
             }
         }
     }
-    Fr inv = warp_inverse(run);  // 1 / (product of all the thread's denominators)
+    static_assert(kThreads == 128, "block_batch_inverse<F, 4> expects 4 warps");
+    Fr inv = block_batch_inverse<F, 4>(run);  // 1 / (product of all the thread's denominators); one inversion per CTA
 #pragma unroll
     for (int i = kPer - 1; i >= 0; i--) {
         const size_t j = base + (size_t)i * kThreads;

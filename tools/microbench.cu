@@ -97,6 +97,14 @@ __global__ void k_madd_loop(G1Affine* pts, G1Xyzz* out, int iters, int npts) {
     out[t] = acc;
 }
 
+// latency of ONE binary-GCD inversion on ONE lane per warp (how the batched-affine rounds and the
+// evaluation-form opening use it): every warp inverts its own element, 20 warps per SM
+template <class P>
+__global__ void k_inv_lane0(Fe<P>* data) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if ((threadIdx.x & 31) == 0) data[warp] = fe_inv_gcd<P>(data[warp]);
+}
+
 template <class P>
 __global__ void k_check(const Fe<P>* a, const Fe<P>* b, int n, int* bad) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -222,6 +230,18 @@ int main() {
         MULB("fr_mul", FrParams, 0, 1, 128)
         MULB("fr_mul", FrParams, 0, 2, 128)
         MULB("fr_mul", FrParams, 1, 1, 128)
+        // inversion latency: 148 x 5 CTAs x 4 warps, one lane each
+        {
+            const int nw = sms * 20;
+            Fp* dinv;
+            CK(cudaMalloc(&dinv, sizeof(Fp) * nw));
+            CK(cudaMemcpy(dinv, da, sizeof(Fp) * nw, cudaMemcpyDeviceToDevice));
+            float ms = time_ms([&] { k_inv_lane0<FpParams><<<sms * 5, 128>>>(dinv); });
+            printf("{\"bench\": \"fe_inv_gcd<Fp> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FrParams><<<sms * 5, 128>>>((Fr*)dinv); });
+            printf("{\"bench\": \"fe_inv_gcd<Fr> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
+            cudaFree(dinv);
+        }
         // mixed additions
         G1Affine* pts;
         G1Xyzz* out;
