@@ -23,7 +23,8 @@ namespace fb {
 namespace {
 
 using F = FrParams;
-constexpr int kPer = 4;          // elements per thread in the inversion kernel
+constexpr int kPer = 4;          // fewest elements per thread in the inversion kernel (small inputs)
+constexpr int kInvBlocksPerSM = 4;  // its grid is capped at one resident wave
 constexpr int kThreads = 128;
 constexpr int kDotPer = 8;       // elements per thread in the dot-product kernel
 constexpr uint32_t kNoIndex = 0xffffffffu;
@@ -61,42 +62,38 @@ __global__ void k_ef_consts(EfArgs a) {
 }
 
 // inv_j = 1/(w^j - alpha) (0 where w^j = alpha, whose index goes to kidx) and h_j = w^j inv_j.
-// Thread t of a block owns elements base + i*kThreads + t, so a warp touches contiguous runs.
+// ONE resident wave: thread t owns elements i*nt + t (a warp touches contiguous runs), walks them once
+// forwards keeping the running product of its denominators (the product before element j is parked in
+// inv[j], w^j in h[j]), the CTA shares one inversion, and the walk back peels the inverses off.  The
+// inversion is a ~50-80 us dependent chain on one lane: it is paid once per launch, not once per 512
+// elements in each of several waves (that form took 373 us at 2^20).
 __global__ void __launch_bounds__(kThreads) k_ef_inverse(EfArgs a) {
-    const size_t base = (size_t)blockIdx.x * (kThreads * kPer) + threadIdx.x;
-    const Fr alpha = *a.alpha;
-    Fr w[kPer], pre[kPer];
-    bool zero[kPer];
-    Fr run = Fr::one();
-#pragma unroll
-    for (int i = 0; i < kPer; i++) {
-        const size_t j = base + (size_t)i * kThreads;
-        zero[i] = true;
-        w[i] = Fr::one();
-        if (j < a.n) {
-            w[i] = omega_pow(a, j);
-            Fr d = fe_sub<F>(w[i], alpha);
-            if (d.is_zero()) *a.kidx = (uint32_t)j;
-            else {
-                zero[i] = false;
-                pre[i] = run;  // product of the thread's earlier denominators
-                run = fe_mul<F>(run, d);
-            }
-        }
-    }
     static_assert(kThreads == 128, "block_batch_inverse<F, 4> expects 4 warps");
-    Fr inv = block_batch_inverse<F, 4>(run);  // 1 / (product of all the thread's denominators); one inversion per CTA
-#pragma unroll
-    for (int i = kPer - 1; i >= 0; i--) {
-        const size_t j = base + (size_t)i * kThreads;
-        if (j >= a.n) continue;
+    const size_t nt = (size_t)gridDim.x * kThreads;
+    const size_t t = (size_t)blockIdx.x * kThreads + threadIdx.x;
+    const Fr alpha = *a.alpha;
+    Fr run = Fr::one();
+    for (size_t j = t; j < a.n; j += nt) {
+        const Fr w = omega_pow(a, j);
+        const Fr d = fe_sub<F>(w, alpha);
+        a.h[j] = w;
+        a.inv[j] = run;
+        if (d.is_zero()) *a.kidx = (uint32_t)j;
+        else run = fe_mul<F>(run, d);
+    }
+    Fr inv = block_batch_inverse<F, 4>(run);  // 1 / (product of all the thread's denominators)
+    if (t >= a.n) return;
+    for (size_t j = t + ((a.n - 1 - t) / nt) * nt;; j -= nt) {  // the thread's last element, then backwards
+        const Fr w = a.h[j];
+        const Fr d = fe_sub<F>(w, alpha);
         Fr v = Fr::zero();
-        if (!zero[i]) {
-            v = fe_mul<F>(inv, pre[i]);
-            inv = fe_mul<F>(inv, fe_sub<F>(w[i], alpha));
+        if (!d.is_zero()) {
+            v = fe_mul<F>(inv, a.inv[j]);
+            inv = fe_mul<F>(inv, d);
         }
         a.inv[j] = v;
-        a.h[j] = fe_mul<F>(w[i], v);
+        a.h[j] = fe_mul<F>(w, v);
+        if (j < nt) break;
     }
 }
 
@@ -184,7 +181,11 @@ void evalform_open(const NttTables& tab, const Fr* d_evals, size_t n, size_t bat
     a.qhat = d_qhat;
     prof_mark("open.evalform", st);
     (++g_launches, k_ef_consts<<<1, 1, 0, st>>>(a));
-    (++g_launches, k_ef_inverse<<<(unsigned)((n + kThreads * kPer - 1) / (kThreads * kPer)), kThreads, 0, st>>>(a));
+    {
+        size_t blocks = (n + kThreads * kPer - 1) / (kThreads * kPer);
+        if (blocks > (size_t)kNumSMs * kInvBlocksPerSM) blocks = (size_t)kNumSMs * kInvBlocksPerSM;  // one resident wave
+        (++g_launches, k_ef_inverse<<<(unsigned)blocks, kThreads, 0, st>>>(a));
+    }
     (++g_launches, k_ef_dot<<<dim3(a.nblk, (unsigned)(batch + 1)), kThreads, 0, st>>>(a));
     (++g_launches, k_ef_finish<<<(unsigned)(batch + 1), kThreads, 0, st>>>(a));
     (++g_launches, k_ef_quotient<<<dim3((unsigned)((n + kThreads - 1) / kThreads), (unsigned)batch), kThreads, 0, st>>>(a));
