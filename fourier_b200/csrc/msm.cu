@@ -575,13 +575,21 @@ struct BitsArgs {
     const G1Xyzz* R;  // split: [set][2^h] row sums
     int k, l, h;      // l == 0: direct
     G1Xyzz* Q;        // [set][k+1]: per-bit sums by overall weight, Q[k] = plain total
+    uint32_t njobs;   // sets * (k + 1)
 };
 
 constexpr int kBitsThreads = 128;
 
+// One job per (set, bit), G threads per job and kBitsThreads / G jobs per CTA: G = 32 when a job has at most
+// 32 addends (the row MSMs of the bivariate path: 2^10 sets of 2^11 buckets, 12288 jobs of 16-32 addends,
+// where a 128-thread CTA per job left three warps of four idle at every barrier), else the whole CTA.
+template <int G>
 __global__ void __launch_bounds__(kBitsThreads) k_bits(BitsArgs a) {
     __shared__ G1Xyzz sm[kBitsThreads];
-    const uint32_t set = blockIdx.x / (a.k + 1), q = blockIdx.x % (a.k + 1);
+    const uint32_t job = blockIdx.x * (kBitsThreads / G) + threadIdx.x / G;
+    const uint32_t tj = threadIdx.x % G;
+    const bool live = job < a.njobs;
+    const uint32_t set = job / (a.k + 1), q = job % (a.k + 1);
     const G1Xyzz* src;
     uint32_t n;
     int bit;  // -1: plain total
@@ -598,22 +606,22 @@ __global__ void __launch_bounds__(kBitsThreads) k_bits(BitsArgs a) {
         n = 1u << a.h;
         bit = (int)q < a.k ? (int)q - a.l : -1;
     }
-    const uint32_t cnt = bit < 0 ? n : n >> 1;
+    const uint32_t cnt = live ? (bit < 0 ? n : n >> 1) : 0u;
     G1Xyzz acc = G1Xyzz::inf();
-    for (uint32_t i = threadIdx.x; i < cnt; i += kBitsThreads) {
+    for (uint32_t i = tj; i < cnt; i += G) {
         uint32_t idx = bit < 0 ? i : (((i >> bit) << (bit + 1)) | (1u << bit) | (i & ((1u << bit) - 1u)));
         g1_add(acc, src[idx]);
     }
     sm[threadIdx.x] = acc;
-    for (uint32_t s = kBitsThreads / 2; s > 0; s >>= 1) {
+    for (uint32_t s = G / 2; s > 0; s >>= 1) {
         __syncthreads();
-        if (threadIdx.x < s && threadIdx.x + s < cnt) {
+        if (tj < s && tj + s < cnt) {
             G1Xyzz x = sm[threadIdx.x];
             g1_add(x, sm[threadIdx.x + s]);
             sm[threadIdx.x] = x;
         }
     }
-    if (threadIdx.x == 0) a.Q[(size_t)set * (a.k + 1) + q] = sm[0];
+    if (live && tj == 0) a.Q[job] = sm[threadIdx.x];
 }
 
 // S[set] = sum_{j<k} 2^j * Q[set][j] + Q[set][k].  One block of 32 threads per set.
@@ -952,7 +960,13 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     G1Xyzz* Q = s.misc.as<G1Xyzz>((size_t)nsets * (k + 1) + nsets);
     G1Xyzz* S = Q + (size_t)nsets * (k + 1);
     ba.Q = Q;
-    (++fb::g_launches, k_bits<<<nsets * (k + 1), kBitsThreads, 0, st>>>(ba));
+    ba.njobs = (uint32_t)(nsets * (k + 1));
+    {
+        // most addends of a job, log2: column bits have 2^(l-1), row bits 2^(h-1), the plain total 2^h (2^k when direct)
+        const int widest = ba.l ? (ba.l - 1 > ba.h ? ba.l - 1 : ba.h) : k;
+        if (widest <= 5) (++fb::g_launches, k_bits<32><<<(ba.njobs + kBitsThreads / 32 - 1) / (kBitsThreads / 32), kBitsThreads, 0, st>>>(ba));
+        else (++fb::g_launches, k_bits<kBitsThreads><<<ba.njobs, kBitsThreads, 0, st>>>(ba));
+    }
     prof_mark("msm.finish", st);
     (++fb::g_launches, k_bit_combine<<<nsets, 32, 0, st>>>(Q, k, tab ? d_out : S));
     if (!tab) (++fb::g_launches, k_window_combine<<<(unsigned)batch, 64, 0, st>>>(S, (uint32_t)nwin, c, d_out));
