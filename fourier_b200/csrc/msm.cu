@@ -580,8 +580,8 @@ struct BitsArgs {
 
 constexpr int kBitsThreads = 128;
 
-// One job per (set, bit), G threads per job and kBitsThreads / G jobs per CTA: G = 32 when a job has at most
-// 32 addends (the row MSMs of the bivariate path: 2^10 sets of 2^11 buckets, 12288 jobs of 16-32 addends,
+// One job per (set, bit), G threads per job and kBitsThreads / G jobs per CTA: G = 32 (64) when a job has at most
+// 32 (64) addends (the row MSMs of the bivariate path: 2^10 sets of 2^11 buckets, 12288 jobs of 16-32 addends,
 // where a 128-thread CTA per job left three warps of four idle at every barrier), else the whole CTA.
 template <int G>
 __global__ void __launch_bounds__(kBitsThreads) k_bits(BitsArgs a) {
@@ -788,7 +788,16 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     // Measured on B200 (profiles/): three rounds ahead of the XYZZ kernel are ~8% faster than the
     // XYZZ kernel alone at 2^20 points (pass 2 runs at the multiplier's rate, pass 1 of the first
     // round is bound by the gather); small inputs do not amortise the per-round inversion.
-    int rounds = rounds_env >= 0 ? rounds_env : ((entries >= (4u << 20) && entries / nbuckets >= 8) ? 3 : 0);
+    // Jobs of >= 64 M entries (the 2^24-point MSM, the 2^10 batched rows) amortise two more rounds when the buckets
+    // are deep enough: 2^24 points 217.5 -> 222.1 Mpts/s, bivariate rows 69.1 -> 67.8 ms; at 2^20 points (16 M
+    // entries) a fourth round costs 0.1 ms (profiles/r1_v7_sweeps.txt).
+    int rounds = 0;
+    if (entries >= (4u << 20) && entries / nbuckets >= 8) {
+        rounds = 3;
+        if (entries >= (64u << 20) && entries / nbuckets >= 64) rounds = 5;
+        else if (entries >= (64u << 20) && entries / nbuckets >= 32) rounds = 4;
+    }
+    if (rounds_env >= 0) rounds = rounds_env;
     if (rounds > 8) rounds = 8;
     uint32_t* sorted = s.sorted.as<uint32_t>(entries);
 
@@ -965,6 +974,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         // most addends of a job, log2: column bits have 2^(l-1), row bits 2^(h-1), the plain total 2^h (2^k when direct)
         const int widest = ba.l ? (ba.l - 1 > ba.h ? ba.l - 1 : ba.h) : k;
         if (widest <= 5) (++fb::g_launches, k_bits<32><<<(ba.njobs + kBitsThreads / 32 - 1) / (kBitsThreads / 32), kBitsThreads, 0, st>>>(ba));
+        else if (widest == 6) (++fb::g_launches, k_bits<64><<<(ba.njobs + kBitsThreads / 64 - 1) / (kBitsThreads / 64), kBitsThreads, 0, st>>>(ba));
         else (++fb::g_launches, k_bits<kBitsThreads><<<ba.njobs, kBitsThreads, 0, st>>>(ba));
     }
     prof_mark("msm.finish", st);
