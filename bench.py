@@ -256,7 +256,8 @@ def own_arm(args):
             "roofline_int": {"kernel": "whole MSM (digits+sort+accumulate+reduce)", "bound": "int (IMAD.WIDE)",
                              "achieved": ach_mad / 1e12, "peak": int_peak / 1e12, "unit": "T wide-MAD/s",
                              "frac": ach_mad / int_peak, "peak_source": int_src,
-                             "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp},
+                             "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp,
+                             "note": "work-equivalent rate, not pipe utilisation: the accounting credits 10 Fp multiplies per point and window (XYZZ mixed addition), the batched-affine rounds spend 6, so frac can reach or pass 1; ncu puts the round kernels at 74-82 % of the multiplier pipe (profiles/r1_v7_ncu_k_round_pass.txt)"},
             "roofline_field": {"kernel": "field half of worker_open: " + ("evalform_open (y = p(alpha) and the quotient's evaluations, "
                                "no transform)" if field_ms and not ntt_ms else "iNTT + Horner/quotient scan + NTT"),
                                "bound": "hbm", "achieved": field_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",

@@ -248,7 +248,8 @@ def run_msm(args):
                          "note": "algorithmic bytes = 128 B/point; the binding limit is the integer pipe, see roofline_int"},
             "roofline_int": {"kernel": "whole MSM", "bound": "int (IMAD.WIDE)", "achieved": n * mad_pp / (ms_dev * 1e-3) / 1e12,
                              "peak": world * int_peak / 1e12, "unit": "T wide-MAD/s", "frac": n * mad_pp / (ms_dev * 1e-3) / (world * int_peak),
-                             "peak_source": int_src, "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp},
+                             "peak_source": int_src, "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp,
+                             "note": "work-equivalent rate, not pipe utilisation: the accounting credits 10 Fp multiplies per point and window (XYZZ mixed addition), the batched-affine rounds spend 6, so frac can reach or pass 1; ncu puts the round kernels at 74-82 % of the multiplier pipe (profiles/r1_v7_ncu_k_round_pass.txt)"},
             "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
             "result": {"msm": res.hex()},
         }
@@ -377,7 +378,8 @@ def run_bipoly(args):
             "roofline_int": {"kernel": "row MSMs (commit + open)", "bound": "int (IMAD.WIDE)",
                              "achieved": (pts / world) * 66000 / (msm_ms * 1e-3) / 1e12 if msm_ms else None, "peak": int_peak / 1e12,
                              "unit": "T wide-MAD/s", "frac": (pts / world) * 66000 / (msm_ms * 1e-3) / int_peak if msm_ms else None,
-                             "peak_source": int_src, "work": "66000 wide-MAD/point at the fixed accounting window for 2^12 rows (SURVEY 8d)"},
+                             "peak_source": int_src, "work": "66000 wide-MAD/point at the fixed accounting window for 2^12 rows (SURVEY 8d)",
+                             "note": "work-equivalent rate, not pipe utilisation: the accounting credits 10 Fp multiplies per point and window (XYZZ mixed addition), the batched-affine rounds spend 6, so frac can reach or pass 1; ncu puts the round kernels at 74-82 % of the multiplier pipe (profiles/r1_v7_ncu_k_round_pass.txt)"},
             "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
             "extra": {"msm_mpts_per_s": pts / (ms_dev * 1e-3) / 1e6},
             "result": {"master_commit": hres[3].hex(), "z": hres[4].hex(), "pi0": hres[5].hex(), "pi1": hres[6].hex()},
