@@ -7,7 +7,7 @@
 
 namespace fb {
 
-unsigned long long g_launches = 0;
+std::atomic<unsigned long long> g_launches{0};
 thread_local Prof* g_prof = nullptr;
 
 int ctx_fail(fb_ctx* c, int code, const std::string& msg) {
@@ -144,7 +144,7 @@ int fb_ctx_set_window(fb_ctx* c, int w) {
     return FB_OK;
 }
 
-uint64_t fb_launch_count(const fb_ctx*) { return g_launches; }
+uint64_t fb_launch_count(const fb_ctx*) { return g_launches.load(); }
 
 int fb_prof_enable(fb_ctx* c, int on) {
     if (!c) return FB_ERR_ARG;

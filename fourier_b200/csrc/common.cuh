@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <string>
@@ -14,7 +15,7 @@
 namespace fb {
 
 constexpr int kNumSMs = 148;  // B200
-extern unsigned long long g_launches;  // kernel launches issued by this library (api.cu)
+extern std::atomic<unsigned long long> g_launches;  // kernel launches issued by this library (api.cu); contexts on several host threads count together
 
 struct CudaError {
     std::string msg;

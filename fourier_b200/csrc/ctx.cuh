@@ -49,7 +49,7 @@ struct fb_ctx {
 
 namespace fb {
 
-extern unsigned long long g_launches;
+extern std::atomic<unsigned long long> g_launches;
 
 struct CtxGuard {
     fb_ctx* c;

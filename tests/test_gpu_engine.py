@@ -346,3 +346,49 @@ def test_open_short_rows(small, length):
         y, pi = b.worker_open(0, coeffs, alpha)
         oy, opi = o.worker_open(0, coeffs, alpha)
         assert y == oy.to_bytes(32, "big") and pi == bls.g1_compress(opi)
+
+
+def test_concurrent_calls_on_one_backend(gpu):
+    """rpc.rs:165, 414-416: the backend sits in an Arc and every connection's handler calls it from its own runtime
+    thread, so concurrent calls on one backend are legal.  Eight host threads commit, open, transform and verify on
+    one context at once; every result must equal the one computed serially."""
+    import threading
+    from fourier_b200 import PianoBackend
+    n, m = 12, 2
+    b = PianoBackend(n, m)
+    b.setup(SECRET_X, SECRET_Y)
+    T, M = 1 << (n - m), 1 << m
+    rng = random.Random(77)
+    jobs = []
+    for k in range(8):
+        coeffs = fr_list_to_bytes([rng.randrange(R) for _ in range(T)])
+        jobs.append((k % M, coeffs, rng.randrange(R)))
+
+    def run(job):
+        i, coeffs, alpha = job
+        c = b.worker_commit(i, coeffs)
+        y, pi = b.worker_open(i, coeffs, alpha)
+        f = b.fft(coeffs, inverse=True, left=True)
+        ok = b.worker_verify(i, c, alpha, y, pi)
+        return c, y, pi, f, ok
+
+    serial = [run(j) for j in jobs]
+    assert all(r[4] for r in serial)
+    for _ in range(3):
+        out = [None] * len(jobs)
+        errs = []
+
+        def work(k):
+            try:
+                out[k] = run(jobs[k])
+            except Exception as e:  # noqa: BLE001 - reported below
+                errs.append(e)
+
+        th = [threading.Thread(target=work, args=(k,)) for k in range(len(jobs))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        assert not errs, errs
+        assert out == serial
+    b.close()
