@@ -345,11 +345,14 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
              cudaStream_t st, size_t batch) {
     if (batch == 0) return;
     if (batch > 65535) throw CudaError{"ntt: batch too large"};
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the shared-memory opt-in is per device: a process may hold contexts on several GPUs
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    FB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load()) {
         FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         FB_CUDA(cudaFuncSetAttribute(k_ntt_pass<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true);
     }
     const int log_n = tab.log_n;
     const int d = inverse ? 1 : 0;
