@@ -14,28 +14,53 @@ import json
 import os
 import time
 
-from fourier_b200.benchutil import ClockSampler, load_int_peak, load_peaks
+from fourier_b200.benchutil import ClockSampler, load_fr_mul_rate, load_int_peak, load_peaks
 
 R = 0x73EDA753299D7D483339D80809A1D80553BDA402FFFE5BFEFFFFFFFF00000001
 SECRET_X, SECRET_Y = bytes([1] * 32), bytes([2] * 32)
 DTYPE = "u32 limbs (Fr 255-bit, Fp 381-bit Montgomery, exact integer)"
 
 
+class Env:
+    """One process per GPU: device, the caller's (non-default) torch stream, the NCCL group when N > 1."""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench needs a CUDA device: the product has no CPU path (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.stream = torch.cuda.Stream(device=self.dev)
+        torch.cuda.set_stream(self.stream)
+        assert self.stream.cuda_stream != 0
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, vals):
+        if self.world == 1:
+            return list(vals)
+        t = self.torch.tensor(list(vals), device=self.dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(x) for x in t]
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
 def _env():
-    import torch
-    import torch.distributed as dist
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench needs a CUDA device: the product has no CPU path")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    stream = torch.cuda.Stream(device=dev)
-    torch.cuda.set_stream(stream)
-    return torch, dist, rank, world, local, dev, stream
+    e = Env()
+    return e.torch, e.dist, e.rank, e.world, e.local, e.dev, e.stream
 
 
 def _barrier(torch, dist, world):
@@ -62,13 +87,34 @@ def _dev_fr(torch, be, dev, be_bytes_np):
 
 
 # ------------------------------------------------------------------ config 3: NTT sweep
-def run_ntt(args):
-    torch, dist, rank, world, local, dev, stream = _env()
+def ntt_plan(lg: int, max_r: int = 10):
+    """log2 of the radix of each pass (ntt_make_plan, csrc/ntt.cu): as even as possible over ceil(lg / 10) passes"""
+    npass = max(1, -(-lg // max_r))
+    out, left = [], lg
+    for j in range(npass):
+        r = -(-left // (npass - j))
+        out.append(r)
+        left -= r
+    return out
+
+
+def ntt_fr_muls_per_element(lg: int) -> float:
+    """Fr multiplications the kernel issues per element: half a butterfly multiply per stage, minus the multiplier-free
+    butterflies of the last two stages of every pass (0.75), plus one inter-pass twiddle multiply per non-last pass"""
+    plan = ntt_plan(lg)
+    return sum(max(r * 0.5 - 0.75, 0.0) for r in plan) + (len(plan) - 1)
+
+
+def run_ntt(args, env=None, emit=True):
+    own_env = env is None
+    env = env or Env()
+    torch, dist, rank, world, local, dev, stream = env.torch, env.dist, env.rank, env.world, env.local, env.dev, env.stream
     from fourier_b200 import PianoBackend, synth
     be = PianoBackend(24, 0, device=local)
     be.set_stream(stream.cuda_stream)
     peaks = load_peaks()
-    int_peak, int_src = load_int_peak()
+    int_peak, int_src, _ = load_int_peak()
+    fr_rate = load_fr_mul_rate()
     sweep = {}
     clocks = ClockSampler(local)
     total_launches0 = be.launch_count()
@@ -108,6 +154,8 @@ def run_ntt(args):
             "gelem_per_s": world * n / (res["forward"] * 1e-3) / 1e9,
             "hbm_gbs": n * 64 / (res["forward"] * 1e-3) / 1e9, "hbm_frac": n * 64 / (res["forward"] * 1e-3) / 1e9 / peaks["hbm_gbs"],
             "int_frac": n * mad_per_elem / (res["forward"] * 1e-3) / int_peak,
+            "frac_real": n * ntt_fr_muls_per_element(lg) / (res["forward"] * 1e-3) / fr_rate,
+            "fr_muls_per_element": ntt_fr_muls_per_element(lg),
             "roundtrip_identity": ok, "buffers": nbuf}
         if lg == 24:
             ms_headline = res["forward"]
@@ -128,6 +176,7 @@ def run_ntt(args):
             del h_in, h_out
         del bufs, out, tmp
     clk = clocks.stop()
+    line = None
     if rank == 0:
         n = 1 << 24
         line = {
@@ -146,18 +195,23 @@ def run_ntt(args):
                          "traffic": None, "peak_source": peaks["source"],
                          "note": "algorithmic bytes = 64 B/element (one read + one write); the binding limit is the integer "
                                  "pipe (SURVEY 8d: log2(N)/2 Fr multiplies of 136 wide MADs per element): see sweep[*].int_frac "
-                                 "against " + int_src},
+                                 "against " + int_src + "; sweep[*].frac_real = Fr multiplies actually issued / time / the "
+                                 "fe_mul<Fr> microbenchmark rate"},
             "sweep": sweep,
         }
-        print(json.dumps(line), flush=True)
+        if emit:
+            print(json.dumps(line), flush=True)
     be.close()
-    if world > 1:
-        dist.destroy_process_group()
+    if own_env:
+        env.close()
+    return line
 
 
 # ------------------------------------------------------------------ config 4: one big MSM
-def run_msm(args):
-    torch, dist, rank, world, local, dev, stream = _env()
+def run_msm(args, env=None, emit=True):
+    own_env = env is None
+    env = env or Env()
+    torch, dist, rank, world, local, dev, stream = env.torch, env.dist, env.rank, env.world, env.local, env.dev, env.stream
     from fourier_b200 import PianoBackend, shard, synth
     lg = int(os.environ.get("FB_MSM_LOG", "24"))
     n = 1 << lg
@@ -222,14 +276,20 @@ def run_msm(args):
 
     be.profile(True)
     be.profile_read()
+    be.msm_stats()
     step_device()
     torch.cuda.synchronize()
     prof = be.profile_read()
+    stats = be.msm_stats()
     be.profile(False)
+    wbits, nwin = bases.window()
+    line = None
     if rank == 0:
         peaks = load_peaks()
-        int_peak, int_src = load_int_peak()
+        int_peak, int_src, fp_mul_rate = load_int_peak()
         mad_pp = {24: 39000, 20: 48000}.get(lg, 48000)
+        msm_ms = sum(v[0] for k, v in prof.items() if k.startswith("msm."))
+        muls = stats["round_slots"] * 6 + stats["survivors"] * 10 + stats["buckets"] * 28
         dom = max((k for k in prof if k.startswith("msm.")), key=lambda k: prof[k][0])
         dom_s = prof[dom][0] / max(prof[dom][1], 1) * 1e-3
         line = {
@@ -238,39 +298,49 @@ def run_msm(args):
             "scaling": "strong", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
             "config": {"workload": "one G1 MSM of 2^%d points P_k = s_k*G with random 255-bit scalars (BASELINE config 4)" % lg,
                        "parallelism": "1 GPU" if world == 1 else "point ranges over %d GPUs + all-gather of 96-byte partial sums" % world,
-                       "l2": "inputs larger than L2 (window tables + scalars)", "setup_s": round(setup_s, 2)},
+                       "l2": "inputs larger than L2 (window tables + scalars)", "setup_s": round(setup_s, 2),
+                       "window_bits": wbits, "windows": nwin},
             "e2e": {"value": n / (ms_e2e * 1e-3) / 1e6, "unit": "Mpts/s", "h2d_bytes_per_step": per * 32,
                     "d2h_bytes_per_step": 96 + (world * 96 if world > 1 else 0)},
             "gpu_launches": int(launches), "clocks": clk,
-            "roofline": {"kernel": dom, "bound": "hbm", "achieved": per * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
-                         "unit": "GB/s", "frac": per * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
-                         "peak_source": peaks["source"],
-                         "note": "algorithmic bytes = 128 B/point; the binding limit is the integer pipe, see roofline_int"},
-            "roofline_int": {"kernel": "whole MSM", "bound": "int (IMAD.WIDE)", "achieved": n * mad_pp / (ms_dev * 1e-3) / 1e12,
-                             "peak": world * int_peak / 1e12, "unit": "T wide-MAD/s", "frac": n * mad_pp / (ms_dev * 1e-3) / (world * int_peak),
-                             "peak_source": int_src, "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp,
-                             "note": "work-equivalent rate, not pipe utilisation: the accounting credits 10 Fp multiplies per point and window (XYZZ mixed addition), the batched-affine rounds spend 6, so frac can reach or pass 1; ncu puts the round kernels at 74-82 % of the multiplier pipe (profiles/r1_v7_ncu_k_round_pass.txt)"},
+            "roofline": {"kernel": "whole MSM pipeline", "bound": "int", "achieved": n * mad_pp / (ms_dev * 1e-3) / 1e12,
+                         "peak": world * int_peak / 1e12, "unit": "T wide-MAD/s", "frac": n * mad_pp / (ms_dev * 1e-3) / (world * int_peak),
+                         "frac_real": muls / (msm_ms * 1e-3) / fp_mul_rate if msm_ms else None,
+                         "peak_source": int_src, "traffic": None,
+                         "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d)" % mad_pp,
+                         "real_work": {"fp_muls_rank0": muls, **stats, "formula": "6 x slots + 10 x survivors + 28 x buckets"},
+                         "note": "frac credits 10 Fp multiplies per (point, window) whatever the kernels spend (6 in the affine "
+                                 "rounds): a work-equivalent rate; frac_real = Fp multiplies issued / time / the fe_mul rate (rank 0)"},
+            "roofline_hbm": {"kernel": dom, "bound": "hbm", "achieved": per * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
+                             "unit": "GB/s", "frac": per * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                             "peak_source": peaks["source"], "note": "algorithmic bytes = 128 B/point; not the binding bound"},
             "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
             "result": {"msm": res.hex()},
         }
-        if args.check:  # known discrete logs: sum k_i * s_i in the exponent, one scalar multiplication in the oracle
+        if args.check or not emit:  # known discrete logs: sum k_i * s_i in the exponent, one scalar multiplication in the oracle
             from oracle import bls12_381 as bls
             acc = 0
             for lo in range(0, n, 1 << 18):
-                ss = synth.fr_ints(21, 1 << 18, lo)
-                ks = synth.fr_ints(22, 1 << 18, lo)
-                acc = (acc + sum(a * b for a, b in zip(ss, ks))) % R
+                cnt = min(1 << 18, n - lo)
+                sb = synth.fr_words(21, cnt, lo).astype("<u8").tobytes()
+                kb = synth.fr_words(22, cnt, lo).astype("<u8").tobytes()
+                acc = (acc + sum(int.from_bytes(sb[32 * i:32 * i + 32], "little") * int.from_bytes(kb[32 * i:32 * i + 32], "little")
+                                 for i in range(cnt))) % R
             line["parity"] = {"known_dlog_match": bls.g1_compress(bls.g1_mul(bls.G1_GEN, acc)) == res}
-        print(json.dumps(line), flush=True)
+        if emit:
+            print(json.dumps(line), flush=True)
     bases.free()
     be.close()
-    if world > 1:
-        dist.destroy_process_group()
+    if own_env:
+        env.close()
+    return line
 
 
 # ------------------------------------------------------------------ config 5: bivariate rows
-def run_bipoly(args):
-    torch, dist, rank, world, local, dev, stream = _env()
+def run_bipoly(args, env=None, emit=True):
+    own_env = env is None
+    env = env or Env()
+    torch, dist, rank, world, local, dev, stream = env.torch, env.dist, env.rank, env.world, env.local, env.dev, env.stream
     from fourier_b200 import PianoBackend, shard, synth
     n_scale = int(os.environ.get("FB_BIPOLY_SCALE", "22"))
     m_scale = int(os.environ.get("FB_BIPOLY_MSCALE", "10"))
@@ -291,9 +361,12 @@ def run_bipoly(args):
     d_c, d_y, d_p = d_out[:rows * 48], d_out[rows * 48:rows * 80], d_out[rows * 80:]
     gathered = torch.zeros(world * rows * 128, dtype=torch.uint8, device=dev) if world > 1 else None
 
+    be.set_lanes(int(os.environ.get("FB_BENCH_LANES", "1")))
+
     def step_device():
         be.dev_commit_rows(row0, rows, d_coeffs, T, d_c)
         be.dev_open_rows(row0, rows, d_coeffs, T, d_alpha, d_y, d_p)
+        be.join()
         if world > 1:
             dist.all_gather_into_tensor(gathered, d_out)
 
@@ -343,16 +416,22 @@ def run_bipoly(args):
     ms_e2e = (time.perf_counter() - t0) * 1e3 / args.steps
     ms_dev, ms_e2e = _max_over_ranks(torch, dist, world, dev, [ms_dev, ms_e2e])
 
+    be.set_lanes(1)
     be.profile(True)
     be.profile_read()
+    be.msm_stats()
     step_device()
     torch.cuda.synchronize()
     prof = be.profile_read()
+    stats = be.msm_stats()
     be.profile(False)
+    wbits, nwin = be.window()
+    line = None
     if rank == 0:
         assert (hres[0], hres[1], hres[2]) == (cs, ys, ps), "host-API and device-resident results differ"
         peaks = load_peaks()
-        int_peak, int_src = load_int_peak()
+        int_peak, int_src, fp_mul_rate = load_int_peak()
+        muls = stats["round_slots"] * 6 + stats["survivors"] * 10 + stats["buckets"] * 28
         pts = 2 * M * T  # points through the MSMs of one step (commit + open)
         msm_ms = sum(v[0] for k, v in prof.items() if k.startswith("msm."))
         dom = max((k for k in prof if k.startswith("msm.")), key=lambda k: prof[k][0])
@@ -366,20 +445,23 @@ def run_bipoly(args):
                        "parallelism": "1 GPU" if world == 1 else "rows sharded over %d GPUs (%d rows each), all-gather of "
                                       "128 bytes per row, master step on rank 0" % (world, rows),
                        "l2": "inputs larger than L2 (window tables of the local rows + coefficient matrix)",
-                       "srs_setup_s": round(setup_s, 2)},
+                       "srs_setup_s": round(setup_s, 2), "window_bits": wbits, "windows": nwin,
+                       "lanes": int(os.environ.get("FB_BENCH_LANES", "1"))},
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * rows * T * 32 + 32,
                     "d2h_bytes_per_step": rows * 128 + (world * rows * 128 if world > 1 else 0) + 128,
                     "includes": "master_commit + master_open on rank 0"},
             "gpu_launches": int(launches), "clocks": clk,
-            "roofline": {"kernel": dom, "bound": "hbm", "achieved": rows * T * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
-                         "unit": "GB/s", "frac": rows * T * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
-                         "peak_source": peaks["source"],
-                         "note": "algorithmic bytes = 128 B/point; the binding limit is the integer pipe, see roofline_int"},
-            "roofline_int": {"kernel": "row MSMs (commit + open)", "bound": "int (IMAD.WIDE)",
-                             "achieved": (pts / world) * 66000 / (msm_ms * 1e-3) / 1e12 if msm_ms else None, "peak": int_peak / 1e12,
-                             "unit": "T wide-MAD/s", "frac": (pts / world) * 66000 / (msm_ms * 1e-3) / int_peak if msm_ms else None,
-                             "peak_source": int_src, "work": "66000 wide-MAD/point at the fixed accounting window for 2^12 rows (SURVEY 8d)",
-                             "note": "work-equivalent rate, not pipe utilisation: the accounting credits 10 Fp multiplies per point and window (XYZZ mixed addition), the batched-affine rounds spend 6, so frac can reach or pass 1; ncu puts the round kernels at 74-82 % of the multiplier pipe (profiles/r1_v7_ncu_k_round_pass.txt)"},
+            "roofline": {"kernel": "row MSMs (commit + open), whole pipeline", "bound": "int",
+                         "achieved": (pts / world) * 66000 / (msm_ms * 1e-3) / 1e12 if msm_ms else None, "peak": int_peak / 1e12,
+                         "unit": "T wide-MAD/s", "frac": (pts / world) * 66000 / (msm_ms * 1e-3) / int_peak if msm_ms else None,
+                         "frac_real": muls / (msm_ms * 1e-3) / fp_mul_rate if msm_ms else None, "traffic": None,
+                         "peak_source": int_src, "work": "66000 wide-MAD/point at the fixed accounting window for 2^12 rows (SURVEY 8d)",
+                         "real_work": {"fp_muls_rank0": muls, **stats, "formula": "6 x slots + 10 x survivors + 28 x buckets"},
+                         "note": "frac credits 10 Fp multiplies per (point, window) whatever the kernels spend (6 in the affine "
+                                 "rounds): a work-equivalent rate; frac_real = Fp multiplies issued / time / the fe_mul rate (rank 0)"},
+            "roofline_hbm": {"kernel": dom, "bound": "hbm", "achieved": rows * T * 128 / dom_s / 1e9, "peak": peaks["hbm_gbs"],
+                             "unit": "GB/s", "frac": rows * T * 128 / dom_s / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                             "peak_source": peaks["source"], "note": "algorithmic bytes = 128 B/point; not the binding bound"},
             "phases_ms": {k: round(v[0], 4) for k, v in sorted(prof.items())},
             "extra": {"msm_mpts_per_s": pts / (ms_dev * 1e-3) / 1e6},
             "result": {"master_commit": hres[3].hex(), "z": hres[4].hex(), "pi0": hres[5].hex(), "pi1": hres[6].hex()},
@@ -405,10 +487,57 @@ def run_bipoly(args):
                     (bls.g1_decompress(hres[5]), bls.g1_decompress(hres[6]))))
             except Exception as exc:  # the oracle's pairing needs the G2 side of the setup
                 line["parity"]["master_verify"] = "skipped: %s" % exc
-        print(json.dumps(line), flush=True)
+        if emit:
+            print(json.dumps(line), flush=True)
     be.close()
-    if world > 1:
-        dist.destroy_process_group()
+    if own_env:
+        env.close()
+    return line
+
+
+# ------------------------------------------------------------------ the setup-point loader
+def srs_load_lines(be, n_scale, m_scale, tag=None):
+    """Throughput of PianoSettings::load_setup_from_file's replacement (piano.rs:711-846): the context `be` (whole SRS
+    resident) writes its setup in both encodings to a file, and a fresh context loads each: file read, H2D through the
+    pinned ring, on-GPU decompression (one Fp square root per point) / deserialisation, window-table build."""
+    import tempfile
+    from fourier_b200 import PianoBackend
+    M, T = 1 << m_scale, 1 << (n_scale - m_scale)
+    npts = 1 + T + M + M * T
+    out = {}
+    tag = tag or ("n%d_m%d" % (n_scale, m_scale))
+    with tempfile.TemporaryDirectory() as d:
+        for compressed in (True, False):
+            path = os.path.join(d, "setup")
+            be.save_setup_to_file(path, compressed)
+            size = os.path.getsize(path)
+            b2 = PianoBackend(n_scale, m_scale)
+            t0 = time.perf_counter()
+            b2.load_setup_from_file(path, compressed)
+            ms = (time.perf_counter() - t0) * 1e3
+            b2.set_window(-1)  # no tables: isolates read + upload + decode
+            t0 = time.perf_counter()
+            b2.load_setup_from_file(path, compressed)
+            ms_nt = (time.perf_counter() - t0) * 1e3
+            same = b2.setup_to_bytes(True)[:4096] == be.setup_to_bytes(True)[:4096] if npts < (1 << 21) else None
+            b2.close()
+            out["%s_%s" % (tag, "compressed" if compressed else "uncompressed")] = {
+                "file_mib": size / 2**20, "points": npts, "ms": ms, "points_per_s": npts / (ms * 1e-3),
+                "ms_without_tables": ms_nt, "points_per_s_without_tables": npts / (ms_nt * 1e-3),
+                "gib_per_s_without_tables": size / 2**30 / (ms_nt * 1e-3), "prefix_matches": same}
+            os.unlink(path)
+    return out
+
+
+def srs_load_c5(env):
+    """The C5 file (n=22, m=10: 2^22 + 2^12 + 2^10 + 1 points, 192 MiB compressed)."""
+    from fourier_b200 import PianoBackend
+    be = PianoBackend(22, 10, device=env.local)
+    be.setup(SECRET_X, SECRET_Y)
+    out = srs_load_lines(be, 22, 10)
+    be.close()
+    env.torch.cuda.empty_cache()
+    return out
 
 
 RUN = {"ntt": run_ntt, "msm": run_msm, "bipoly": run_bipoly}

@@ -23,6 +23,11 @@ SYMBOLS = [
     ("fb_ctx_set_stream", C.c_int, [_ctx, C.c_void_p]),
     ("fb_ctx_sync", C.c_int, [_ctx]),
     ("fb_ctx_set_window", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_get_window", C.c_int, [_ctx, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    ("fb_ctx_set_open_mode", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_set_staging", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_set_lanes", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_join", C.c_int, [_ctx]),
     ("fb_srs_generate", C.c_int, [_ctx, _u8p, _u8p, C.c_uint64, C.c_uint64]),
     ("fb_srs_load_file", C.c_int, [_ctx, C.c_char_p, C.c_int, C.c_uint64, C.c_uint64]),
     ("fb_srs_load_bytes", C.c_int, [_ctx, _u8p, C.c_size_t, C.c_int, C.c_uint64, C.c_uint64]),
@@ -44,6 +49,7 @@ SYMBOLS = [
     ("fb_bases_from_scalars", C.c_int, [_ctx, _u8p, C.c_uint64, C.POINTER(_bases)]),
     ("fb_bases_precompute", C.c_int, [_ctx, _bases, C.c_int]),
     ("fb_bases_get", C.c_int, [_ctx, _bases, C.c_uint64, _u8p]),
+    ("fb_bases_get_window", C.c_int, [_ctx, _bases, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("fb_bases_free", None, [_ctx, _bases]),
     ("fb_msm", C.c_int, [_ctx, _bases, _u8p, C.c_uint64, _u8p]),
     ("fb_msm_partial", C.c_int, [_ctx, _bases, _u8p, C.c_uint64, _u8p]),
@@ -63,9 +69,14 @@ SYMBOLS = [
     ("fb_worker_open_partial", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p]),
     ("fb_dev_worker_commit_partial", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]),
     ("fb_dev_worker_open_partial", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    ("fb_worker_commit_open", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
+    ("fb_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
+    ("fb_dev_worker_commit_open", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    ("fb_dev_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     ("fb_launch_count", C.c_uint64, [_ctx]),
     ("fb_prof_enable", C.c_int, [_ctx, C.c_int]),
     ("fb_prof_read", C.c_int, [_ctx, C.c_char_p, C.c_size_t]),
+    ("fb_msm_stats", C.c_int, [_ctx, C.POINTER(C.c_uint64)]),
 ]
 
 _lib = None

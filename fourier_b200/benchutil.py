@@ -19,13 +19,33 @@ def load_peaks():
     return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
-def load_int_peak():
-    """wide-MAD/s peak of the integer pipe, measured by tools/microbench (profiles/)."""
+def _int_peak_file():
     p = os.path.join(ROOT, "profiles", "int_peak.json")
-    if os.path.exists(p):
-        d = json.load(open(p))
-        return d["wide_mad_per_s"], "measured (profiles/int_peak.json: IMAD.WIDE.U32.X carry chains)"
-    return 148 * 32 * 1.965e9, "nominal 148 SM x 32 IMAD.WIDE/clk x 1.965 GHz"
+    return json.load(open(p)) if os.path.exists(p) else None
+
+
+def load_int_peak():
+    """(wide-MAD/s peak of the integer pipe, where it comes from, Fp multiplications/s of the fe_mul microbenchmark),
+    measured by tools/microbench (profiles/)."""
+    d = _int_peak_file()
+    if d:
+        return (d["wide_mad_per_s"], "measured (profiles/int_peak.json: IMAD.WIDE.U32.X carry chains)",
+                d.get("fp_mul_per_s", d["wide_mad_per_s"] / 288))
+    nominal = 148 * 32 * 1.965e9
+    return nominal, "nominal 148 SM x 32 IMAD.WIDE/clk x 1.965 GHz", nominal / 288
+
+
+def load_fr_mul_rate():
+    d = _int_peak_file()
+    return d.get("fr_mul_per_s", d["wide_mad_per_s"] / 112) if d else 148 * 32 * 1.965e9 / 112
+
+
+def host_cores() -> int:
+    """Cores this process may run on (never the inherited OMP_NUM_THREADS: torchrun exports 1)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 class ClockSampler:

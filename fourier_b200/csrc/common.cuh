@@ -144,13 +144,19 @@ struct MsmBases {
 
 struct MsmScratch {
     DevBuf counts, offsets, cursor, sorted, buckets, block_sums, seg_a, seg_t, order, misc, pts_a, pts_b, pref, where, stage, inv;
+    // while profiling: [0] MSMs, [1] sorted entries, [2] output slots of all affine rounds, [3] survivors that go
+    // through the XYZZ accumulation, [4] buckets  (u64 each; fb_msm_stats)
+    DevBuf stats;
+    bool stats_zeroed = false;
 };
 
 // d_out[b] (device XYZZ) = sum_k scalars[b*len + k] * bases_b[k] for b < batch, where
 // row b's bases start at pts + b*(nwin or 1)*bases.n.  Scalars are device Fr either
 // in Montgomery form (scalars_mont) or canonical little-endian limbs.
+// d_scalars2 != nullptr: batch = 2 over the SAME bases (row 0 = d_scalars, row 1 = d_scalars2, `len` each): the commit
+// and the opening proof of one row in one pass (sort bookkeeping, rounds, reduction and their latency-bound tails once).
 void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
-             MsmScratch& s, cudaStream_t st);
+             MsmScratch& s, cudaStream_t st, const Fr* d_scalars2 = nullptr);
 // table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin, kTableStride bytes per entry
 void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, void* d_out, DevBuf& scratch,
                      cudaStream_t st);

@@ -1,5 +1,25 @@
 // ctx.cuh - the context object behind the C ABI (include/fourier_b200.h).
+//
+// Threading model (SURVEY 8b "Threading"; reference src/rpc.rs:165, 414-416, 502: the backend sits in an
+// Arc and every connection's handler calls it from its own runtime thread).  The SRS, its window tables
+// and the twiddle tables are read-only after setup.  Everything a call writes - scratch in HBM, the error
+// flags, the pinned result / staging buffers, the CUDA stream it launches on - belongs to a LANE:
+//
+//   lanes[0..kMaxLanes)   own streams.  A host call (operands and results in host memory) takes the
+//                         lowest free lane, runs there and synchronises that lane only, so calls from several
+//                         host threads overlap on the GPU.  With fb_ctx_set_lanes(k >= 2) the heavy
+//                         device-resident calls (commit / open / msm / rows) rotate over lanes[0..k): the lane
+//                         forks from the caller's stream, the call returns at once, and fb_ctx_join makes the
+//                         caller's stream wait for everything in flight - a commit and an open of one step then
+//                         run side by side (one MSM's latency-bound phases under the other's multiplier-bound ones).
+//   ulane                 runs on the CALLER's stream S (fb_ctx_set_stream, else a stream of the context): the
+//                         light device-resident utilities (codecs, NTT) and, by default (lanes = 1), the heavy
+//                         device-resident calls too: plain stream order, no join needed.
+//
+// Setup calls (generate / load / free of the SRS) are exclusive: they wait for every call in flight, drain the
+// device and run alone.
 #pragma once
+#include <condition_variable>
 #include <memory>
 
 #include "../../include/fourier_b200.h"
@@ -10,21 +30,53 @@ struct fb_bases {
     fb::G1Affine* raw = nullptr;  // untabulated copy (== b.pts when no table)
 };
 
+struct fb_lane {
+    int index = 0;
+    cudaStream_t stream = nullptr;   // ulane: the caller's stream
+    cudaStream_t own_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_done = nullptr;
+    bool busy = false;   // a host thread is inside a call on this lane
+    bool dirty = false;  // asynchronous work enqueued since the last join
+    fb::MsmScratch msm;
+    fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small, eng_a, eng_b;
+    fb::Prof prof;
+    int* d_err = nullptr;
+    uint8_t* h_pinned = nullptr;  // small pinned result buffer
+    size_t h_pinned_cap = 0;
+    // pinned staging ring for uploads from pageable host memory (a Rust Vec<u8>, Python bytes)
+    uint8_t* h_stage[2] = {nullptr, nullptr};
+    cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+};
+
+constexpr int kMaxLanes = 4;
+constexpr size_t kStageChunk = (size_t)4 << 20;
+
+enum fb_call_kind { FB_CALL_HOST = 0, FB_CALL_ASYNC = 1, FB_CALL_UTIL = 2, FB_CALL_EXCL = 3 };
+
 struct fb_ctx {
     int device = 0;
     uint32_t n = 0, m = 0, t = 0;
     size_t T = 1, M = 1;
-    cudaStream_t own_stream = nullptr;
-    cudaStream_t stream = nullptr;
-    std::mutex mu;
-    std::string err;
+    cudaStream_t own_stream = nullptr;   // S when the caller gave none
+    cudaStream_t user_stream = nullptr;  // S as given through fb_ctx_set_stream
+    std::mutex mu;                       // lane table, call accounting
+    std::condition_variable cv;
+    fb_lane* lanes[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
+    fb_lane* ulane = nullptr;
+    int async_lanes = 1;  // fb_ctx_set_lanes
+    unsigned rr = 0;      // rotation of the asynchronous heavy calls
+    int active = 0;       // calls in flight
+    bool excl = false;
     int window_pref = 0;
+    int open_mode = 0;    // 0: evaluation form (default); 1: the reference's literal iNTT -> eval -> divide -> NTT
+    int staging = 0;      // 0: pinned ring for pageable host input; 1: hand pageable pointers to cudaMemcpyAsync
 
+    std::mutex tab_mu;  // twiddle tables are built on first use, by whichever lane needs them
     fb::TileTwiddles tile_tw;
     bool tile_tw_ready = false;
     std::map<int, fb::NttTables> ntt;
 
-    // SRS (device, affine Montgomery)
+    // SRS (device, affine Montgomery): read-only between setup calls
     bool srs_ready = false;
     uint64_t row0 = 0, nrows = 0;
     uint64_t col0 = 0, ncols = 0;      // resident column range of every row (ncols == T: whole rows)
@@ -38,48 +90,40 @@ struct fb_ctx {
     std::vector<uint8_t> g2_bytes[3];  // g2, g2^tauX, g2^tauY as read / generated (host only)
     int g2_compressed = -1;
 
-    // scratch
-    fb::MsmScratch msm;
-    fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small, eng_a, eng_b;
-    fb::Prof prof;
-    int* d_err = nullptr;
-    uint8_t* h_pinned = nullptr;  // small pinned result buffer
-    size_t h_pinned_cap = 0;
+    cudaStream_t caller_stream() const { return user_stream ? user_stream : own_stream; }
 };
 
 namespace fb {
 
 extern std::atomic<unsigned long long> g_launches;
 
-struct CtxGuard {
-    fb_ctx* c;
-    std::unique_lock<std::mutex> lk;
-    explicit CtxGuard(fb_ctx* ctx) : c(ctx), lk(ctx->mu) {
-        cudaSetDevice(ctx->device);
-        g_prof = &ctx->prof;
-    }
-    ~CtxGuard() {
-        prof_mark("idle", c->stream);
-        g_prof = nullptr;
-    }
-};
-
-const NttTables& ctx_ntt_tables(fb_ctx* c, int log_n);
+const NttTables& ctx_ntt_tables(fb_ctx* c, fb_lane* L, int log_n);
 int ctx_fail(fb_ctx* c, int code, const std::string& msg);
+fb_lane* ctx_acquire(fb_ctx* c, fb_call_kind kind);
+void ctx_release(fb_ctx* c, fb_lane* L, fb_call_kind kind);
+// host -> device copy on the lane's stream; pageable sources go through the lane's pinned ring
+void lane_h2d(fb_ctx* c, fb_lane* L, void* d_dst, const void* h_src, size_t bytes);
 
-// run f(), mapping exceptions to status codes
+// run f(lane), mapping exceptions to status codes
 template <class F>
-int ctx_call(fb_ctx* c, F&& f) {
+int ctx_call(fb_ctx* c, fb_call_kind kind, F&& f) {
     if (!c) return FB_ERR_ARG;
-    CtxGuard g(c);
+    cudaSetDevice(c->device);
+    fb_lane* L = ctx_acquire(c, kind);
+    g_prof = &L->prof;
+    int rc;
     try {
-        return f();
+        rc = f(L);
     } catch (const CudaError& e) {
         cudaGetLastError();
-        return ctx_fail(c, FB_ERR_CUDA, e.msg);
+        rc = ctx_fail(c, FB_ERR_CUDA, e.msg);
     } catch (const std::exception& e) {
-        return ctx_fail(c, FB_ERR_CUDA, e.what());
+        rc = ctx_fail(c, FB_ERR_CUDA, e.what());
     }
+    prof_mark("idle", L->stream);
+    g_prof = nullptr;
+    ctx_release(c, L, kind);
+    return rc;
 }
 
 inline int ilog2_exact(uint64_t v) {  // -1 unless v is a power of two

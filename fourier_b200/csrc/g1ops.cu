@@ -120,8 +120,11 @@ __global__ void __launch_bounds__(128) k_sum_xyzz(const G1Xyzz* __restrict__ in,
     out[t] = acc;
 }
 
-G1Affine* g_gen_table = nullptr;  // per-process (device 0 of the owning context)
-int g_gen_table_dev = -1;
+// generator comb tables, one per device, built once and published only after the build has finished on the
+// device: contexts on several GPUs (or several contexts on one GPU) may run setup concurrently
+constexpr int kMaxDevices = 64;
+G1Affine* g_gen_table[kMaxDevices] = {};
+std::mutex g_gen_table_mu;
 
 }  // namespace
 
@@ -155,15 +158,22 @@ void g1_fixed_base_mul(const Fr* d_scalars, size_t n, G1Affine* d_out, DevBuf& s
     if (!n) return;
     int dev;
     FB_CUDA(cudaGetDevice(&dev));
-    if (!g_gen_table || g_gen_table_dev != dev) {
-        if (g_gen_table) cudaFree(g_gen_table);
-        G1Xyzz* tmp = scratch.as<G1Xyzz>(32 * 255);
-        FB_CUDA(cudaMalloc(&g_gen_table, 32 * 255 * sizeof(G1Affine)));
-        (++fb::g_launches, k_gen_table_xyzz<<<1, 32, 0, st>>>(tmp));
-        (++fb::g_launches, k_to_affine<<<(32 * 255 + 127) / 128, 128, 0, st>>>(tmp, g_gen_table, 32 * 255));
-        g_gen_table_dev = dev;
+    if (dev < 0 || dev >= kMaxDevices) throw CudaError{"device ordinal out of range"};
+    const G1Affine* tab;
+    {
+        std::lock_guard<std::mutex> lk(g_gen_table_mu);
+        if (!g_gen_table[dev]) {
+            G1Xyzz* tmp = scratch.as<G1Xyzz>(32 * 255);
+            G1Affine* t;
+            FB_CUDA(cudaMalloc(&t, 32 * 255 * sizeof(G1Affine)));
+            (++fb::g_launches, k_gen_table_xyzz<<<1, 32, 0, st>>>(tmp));
+            (++fb::g_launches, k_to_affine<<<(32 * 255 + 127) / 128, 128, 0, st>>>(tmp, t, 32 * 255));
+            FB_CUDA(cudaStreamSynchronize(st));  // other streams of this device read it from now on
+            g_gen_table[dev] = t;
+        }
+        tab = g_gen_table[dev];
     }
-    (++fb::g_launches, k_fixed_base_mul<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scalars, n, g_gen_table, d_out));
+    (++fb::g_launches, k_fixed_base_mul<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_scalars, n, tab, d_out));
     FB_CUDA(cudaGetLastError());
 }
 

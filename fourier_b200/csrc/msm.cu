@@ -29,6 +29,8 @@ namespace {
 
 struct DigitArgs {
     const Fr* scalars;
+    const Fr* scalars2;  // shared bases: the second scalar vector (row 1), else nullptr
+    uint32_t row_bases;  // 1: row b has its own bases (b-th row of the table); 0: every row uses the same bases
     uint32_t n;       // total scalars = batch * len
     uint32_t len;     // scalars per row
     uint32_t stride;  // row length of the resident table (index = (row*nwin + w)*stride + col)
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.n) return;
     const uint32_t row = j / a.len, col = j - row * a.len;
-    Fr k = a.scalars[j];
+    Fr k = (a.scalars2 && row) ? a.scalars2[col] : a.scalars[j];
     if (a.mont) k = fe_from_mont<FrParams>(k);
     // k > (r-1)/2: use -(r - k).  The recoded scalar is < 2^254, so ceil(255/c) windows
     // hold every signed digit and the top window never carries out (without this a
@@ -97,7 +99,8 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
             atomicAdd(a.counts + bucket, 1u);
         } else {
             uint32_t slot = atomicAdd(a.counts + bucket, 1u);
-            uint32_t idx = a.tabulated ? (row * a.nwin + (uint32_t)w) * a.stride + col : row * a.stride + col;
+            const uint32_t brow = row * a.row_bases;
+            uint32_t idx = a.tabulated ? (brow * a.nwin + (uint32_t)w) * a.stride + col : brow * a.stride + col;
             a.sorted[slot] = idx | ((neg ^ sneg) << 31);
         }
     }
@@ -414,6 +417,11 @@ __global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
         }
         st_affine(a.out + o, r);
     }
+}
+
+// work counters for the bench's real-multiply accounting (launched only while profiling is on)
+__global__ void k_stat_add(unsigned long long* stats, int slot, const uint32_t* __restrict__ val, unsigned long long add) {
+    stats[slot] += (val ? (unsigned long long)*val : 0ull) + add;
 }
 
 // counts of the next round: ceil(count/2) per bucket (entry nbuckets = 0 closes the scan)
@@ -750,8 +758,10 @@ void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwi
 }
 
 void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
-             MsmScratch& s, cudaStream_t st) {
+             MsmScratch& s, cudaStream_t st, const Fr* d_scalars2) {
     if (batch == 0) return;
+    if (d_scalars2 && batch != 2) throw CudaError{"msm: a second scalar vector means batch = 2"};
+    const bool shared = d_scalars2 != nullptr;
     if (len == 0) {
         FB_CUDA(cudaMemsetAsync(d_out, 0, batch * sizeof(G1Xyzz), st));
         return;
@@ -763,7 +773,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     const int nwin = msm_num_windows(c);
     if (tab && nwin != bases.nwin) throw CudaError{"msm: table window count mismatch"};
     // with a table the entries index [w][k] over the FULL resident row length
-    if ((uint64_t)(tab ? nwin : 1) * bases.n * batch >= (1ull << 31) || n >= (1ull << 32)) throw CudaError{"msm: index space exceeds 31 bits"};
+    if ((uint64_t)(tab ? nwin : 1) * bases.n * (shared ? 1 : batch) >= (1ull << 31) || n >= (1ull << 32)) throw CudaError{"msm: index space exceeds 31 bits"};
     const int k = c - 1;                                // buckets per set = 2^k, index = |digit| - 1
     const uint32_t bpw = 1u << k;
     const uint32_t per_out = tab ? 1u : (uint32_t)nwin;  // bucket sets per output
@@ -805,6 +815,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     FB_CUDA(cudaMemsetAsync(counts, 0, (nbuckets + 1) * sizeof(uint32_t), st));
     DigitArgs a;
     a.scalars = d_scalars;
+    a.scalars2 = d_scalars2;
+    a.row_bases = shared ? 0u : 1u;
     a.n = (uint32_t)n;
     a.len = (uint32_t)len;
     a.stride = (uint32_t)bases.n;
@@ -824,6 +836,17 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     a2.counts = cursor;
     prof_mark("msm.scatter", st);
     (++fb::g_launches, k_digits<1><<<gb, 256, 0, st>>>(a2));
+    const bool stats_on = g_prof && g_prof->on;
+    unsigned long long* stats = s.stats.as<unsigned long long>(8);
+    if (stats_on) {
+        if (!s.stats_zeroed) {
+            FB_CUDA(cudaMemsetAsync(stats, 0, 8 * sizeof(unsigned long long), st));
+            s.stats_zeroed = true;
+        }
+        k_stat_add<<<1, 1, 0, st>>>(stats, 0, nullptr, 1);
+        k_stat_add<<<1, 1, 0, st>>>(stats, 1, offsets + nbuckets, 0);
+        k_stat_add<<<1, 1, 0, st>>>(stats, 4, nullptr, nbuckets);
+    }
 
     // batched-affine halving rounds, then XYZZ accumulation of the survivors
     const uint32_t* off_cur = offsets;
@@ -888,12 +911,14 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
             prof_mark("msm.round_pass2", st);
             (++fb::g_launches, k_round_pass2<0><<<blocks, 128, 0, st>>>(ra));
         }
+        if (stats_on) k_stat_add<<<1, 1, 0, st>>>(stats, 2, off_out + nbuckets, 0);
         pts_cur = reinterpret_cast<const char*>(ra.out);
         stride_cur = (uint32_t)sizeof(G1Affine);
         off_cur = off_out;
         ub = ub_out;
     }
 
+    if (stats_on) k_stat_add<<<1, 1, 0, st>>>(stats, 3, off_cur + nbuckets, 0);
     // accumulate: one wave of resident threads, equal chunks of the (remaining) entries
     prof_mark("msm.accumulate", st);
     static int acc_blocks_per_sm = 0;

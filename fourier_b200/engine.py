@@ -81,6 +81,12 @@ class Bases:
         self._b._chk(self._b._lib.fb_bases_precompute(self._b._ctx, self._h, window_bits))
         return self
 
+    def window(self) -> Tuple[int, int]:
+        """(window bits, number of windows) of the table as built; (0, 0) without one."""
+        c, w = C.c_int(0), C.c_int(0)
+        self._b._chk(self._b._lib.fb_bases_get_window(self._b._ctx, self._h, C.byref(c), C.byref(w)))
+        return c.value, w.value
+
     def point(self, index: int) -> bytes:
         out = C.create_string_buffer(G1_BYTES)
         self._b._chk(self._b._lib.fb_bases_get(self._b._ctx, self._h, index, C.addressof(out)))
@@ -138,6 +144,32 @@ class PianoBackend:
     def sync(self):
         self._chk(self._lib.fb_ctx_sync(self._ctx))
 
+    def set_lanes(self, lanes: int):
+        """lanes >= 2: the heavy dev_* calls rotate over that many internal streams (overlap); see join()."""
+        self._chk(self._lib.fb_ctx_set_lanes(self._ctx, lanes))
+
+    def join(self):
+        """The caller's stream waits (on the device) for every dev_* call in flight on the lanes."""
+        self._chk(self._lib.fb_ctx_join(self._ctx))
+
+    def set_window(self, window_bits: int):
+        """Window bits of the tables built by the next setup / load (0: by row length, -1: no tables)."""
+        self._chk(self._lib.fb_ctx_set_window(self._ctx, window_bits))
+
+    def window(self) -> Tuple[int, int]:
+        """(window bits, number of windows) of the resident row tables as built; (0, 0) without tables."""
+        c, w = C.c_int(0), C.c_int(0)
+        self._chk(self._lib.fb_ctx_get_window(self._ctx, C.byref(c), C.byref(w)))
+        return c.value, w.value
+
+    def set_open_mode(self, literal: bool):
+        """False (default): evaluation-form opening; True: the reference's literal iNTT -> eval -> divide -> NTT."""
+        self._chk(self._lib.fb_ctx_set_open_mode(self._ctx, int(bool(literal))))
+
+    def set_staging(self, direct: bool):
+        """Pageable host inputs: False (default) through the library's pinned ring, True straight to cudaMemcpyAsync."""
+        self._chk(self._lib.fb_ctx_set_staging(self._ctx, int(bool(direct))))
+
     def launch_count(self) -> int:
         return self._lib.fb_launch_count(self._ctx)
 
@@ -150,6 +182,12 @@ class PianoBackend:
         buf = C.create_string_buffer(1 << 16)
         self._chk(self._lib.fb_prof_read(self._ctx, buf, len(buf)))
         return {k: tuple(v) for k, v in json.loads(buf.value.decode()).items()}
+
+    def msm_stats(self) -> dict:
+        """Work counters of the MSMs run while profiling was on (reset by the read)."""
+        out = (C.c_uint64 * 8)()
+        self._chk(self._lib.fb_msm_stats(self._ctx, out))
+        return {"msms": out[0], "entries": out[1], "round_slots": out[2], "survivors": out[3], "buckets": out[4]}
 
     # -- setup (piano.rs:87-122, 883-1037, 649-846) -----------------------------
     def setup(self, secret_x: bytes, secret_y: bytes, row0: int = 0, nrows: int = 0):
@@ -189,6 +227,23 @@ class PianoBackend:
         pi = C.create_string_buffer(G1_BYTES)
         self._chk(self._lib.fb_worker_open(self._ctx, i, _lib.addr(buf), n, _lib.addr(a), C.addressof(y), C.addressof(pi)))
         return y.raw, pi.raw
+
+    def worker_commit_open(self, i: int, coeffs: ScalarVec, alpha) -> Tuple[bytes, bytes, bytes]:
+        """worker_commit + worker_open of the same row in one pass -> (commitment, y, proof)."""
+        buf, n = pack_scalars(coeffs)
+        a = pack_scalar(alpha)
+        cm, y, pi = C.create_string_buffer(G1_BYTES), C.create_string_buffer(FR_BYTES), C.create_string_buffer(G1_BYTES)
+        self._chk(self._lib.fb_worker_commit_open(self._ctx, i, _lib.addr(buf), n, _lib.addr(a), C.addressof(cm),
+                                                  C.addressof(y), C.addressof(pi)))
+        return cm.raw, y.raw, pi.raw
+
+    def worker_commit_open_partial(self, i: int, coeffs: ScalarVec, alpha) -> Tuple[bytes, bytes, bytes]:
+        buf, n = pack_scalars(coeffs)
+        a = pack_scalar(alpha)
+        cm, y, pi = C.create_string_buffer(96), C.create_string_buffer(FR_BYTES), C.create_string_buffer(96)
+        self._chk(self._lib.fb_worker_commit_open_partial(self._ctx, i, _lib.addr(buf), n, _lib.addr(a), C.addressof(cm),
+                                                          C.addressof(y), C.addressof(pi)))
+        return cm.raw, y.raw, pi.raw
 
     def commit_rows(self, row0: int, nrows: int, coeffs: ScalarVec) -> List[bytes]:
         buf, n = pack_scalars(coeffs)
@@ -367,6 +422,14 @@ class PianoBackend:
 
     def dev_worker_commit(self, i: int, d_coeffs, count: int, d_out48):
         self._chk(self._lib.fb_dev_worker_commit(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_out48)))
+
+    def dev_worker_commit_open(self, i: int, d_coeffs, count: int, d_alpha, d_out128):
+        self._chk(self._lib.fb_dev_worker_commit_open(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_alpha),
+                                                      _lib.addr(d_out128)))
+
+    def dev_worker_commit_open_partial(self, i: int, d_coeffs, count: int, d_alpha, d_out224):
+        self._chk(self._lib.fb_dev_worker_commit_open_partial(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_alpha),
+                                                              _lib.addr(d_out224)))
 
     def dev_worker_open(self, i: int, d_coeffs, count: int, d_alpha, d_out80):
         self._chk(self._lib.fb_dev_worker_open(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_alpha),

@@ -14,9 +14,12 @@
  * Montgomery limbs, affine/XYZZ points and window tables never leave the library.
  *
  * A context is bound to ONE CUDA device (one process per GPU); it owns the SRS,
- * the window tables, the twiddle tables and all scratch memory in HBM.  Calls on
- * one context are serialised by an internal mutex, so concurrent callers (the
- * reference runs one tokio task per connection, src/rpc.rs:502) are safe.
+ * the window tables, the twiddle tables and all scratch memory in HBM.  The SRS
+ * and its tables are read-only after setup; every call runs on one of a small
+ * pool of lanes (a CUDA stream with its own scratch, error flags and pinned
+ * buffers), so concurrent callers (the reference keeps the backend in an Arc and
+ * runs one tokio task per connection, src/rpc.rs:165, 414-416, 502) are safe AND
+ * overlap on the GPU.  Setup calls are exclusive.
  * There is no CPU fallback: without a usable CUDA device fb_ctx_create fails.
  */
 #ifndef FOURIER_B200_H
@@ -47,15 +50,39 @@ enum {
  * `device` is the CUDA ordinal.  Fails with FB_ERR_ARG if m > n. */
 int fb_ctx_create(uint32_t n, uint32_t m, int device, fb_ctx** out);
 void fb_ctx_destroy(fb_ctx* ctx);
-const char* fb_last_error(const fb_ctx* ctx); /* message of the last failing call on ctx */
+/* message of the CALLING THREAD's last failing call (thread-local: another thread's
+ * failure cannot overwrite it); valid until that thread's next failing call */
+const char* fb_last_error(const fb_ctx* ctx);
 const char* fb_version(void);
-/* run all work of this context on an existing CUDA stream (cudaStream_t passed as
- * void*), e.g. torch's current stream; NULL restores the context's own stream */
+/* the caller's CUDA stream S (cudaStream_t passed as void*), e.g. torch's current
+ * stream; NULL = a stream of the context.  The device-resident calls (fb_dev_*)
+ * are ordered against S: they see everything enqueued on S before the call, and
+ * with the default fb_ctx_set_lanes(1) they simply run on S. */
 int fb_ctx_set_stream(fb_ctx* ctx, void* cuda_stream);
+/* block the host until every lane and S are idle */
 int fb_ctx_sync(fb_ctx* ctx);
+/* lanes >= 2: the heavy device-resident calls (fb_dev_worker_commit / _open /
+ * _commit_open, fb_dev_commit_rows / _open_rows, fb_dev_msm*, and the _partial
+ * forms) rotate over `lanes` internal streams forked from S and return at once,
+ * so that e.g. the commit and the open of one step overlap on the GPU.  Their
+ * outputs are ordered on S only after fb_ctx_join (a device-side wait, the host
+ * does not block) or fb_ctx_sync.  lanes = 1 (default): plain stream order on S.
+ * Host calls always take a free lane of their own (1..4 concurrent callers). */
+int fb_ctx_set_lanes(fb_ctx* ctx, int lanes);
+int fb_ctx_join(fb_ctx* ctx);
 /* window bits for the resident tables built by the next SRS load/generate
  * (0 = pick from the row length; -1 = no tables: plain Pippenger per call) */
 int fb_ctx_set_window(fb_ctx* ctx, int window_bits);
+/* window bits / number of windows of the resident row tables as built (0, 0: no tables) */
+int fb_ctx_get_window(fb_ctx* ctx, int* window_bits, int* num_windows);
+/* how fb_worker_open forms the quotient's evaluations: 0 (default) straight from the
+ * evaluations (no transform; identical field elements), 1 the reference's literal
+ * sequence iNTT -> eval -> divide -> NTT (piano.rs:193-236).  Same bytes either way. */
+int fb_ctx_set_open_mode(fb_ctx* ctx, int mode);
+/* uploads from PAGEABLE host memory (a Rust Vec<u8>, Python bytes): 0 (default) copy
+ * through the lane's pinned double buffer, 1 hand the pointer to cudaMemcpyAsync.
+ * Pinned / registered sources are always copied directly. */
+int fb_ctx_set_staging(fb_ctx* ctx, int mode);
 
 /* Column sharding (one MSM split over GPUs by point ranges): keep only columns
  * [col0, col0+ncols) of every resident row.  Takes effect at the next SRS
@@ -104,6 +131,16 @@ int fb_worker_commit_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, 
 int fb_worker_open_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
                            uint8_t out_y_be[32], uint8_t out96[96]);
 
+/* commit + open of one row in one pass (extension; the two calls above remain): the
+ * coefficients go up once and both MSMs - same resident row - run as one batch of two
+ * scalar vectors.  Byte-identical to fb_worker_commit followed by fb_worker_open.
+ * len must be a power of two (as for fb_worker_open). */
+int fb_worker_commit_open(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                          uint8_t out_commit48[48], uint8_t out_y_be[32], uint8_t out_proof48[48]);
+int fb_worker_commit_open_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_be, uint64_t len,
+                                  const uint8_t alpha_be[32], uint8_t out_commit96[96], uint8_t out_y_be[32],
+                                  uint8_t out_proof96[96]);
+
 /* ---- engine: master side ------------------------------------------------------
  * replaces PianoBackend::master_commit (piano.rs:164-175): sum of the commitments */
 int fb_master_commit(fb_ctx* ctx, const uint8_t* commitments48, uint64_t count, uint8_t out48[48]);
@@ -147,6 +184,8 @@ int fb_bases_from_points(fb_ctx* ctx, const uint8_t* points, uint64_t count, int
 int fb_bases_from_scalars(fb_ctx* ctx, const uint8_t* scalars_be, uint64_t count, fb_bases** out);
 int fb_bases_precompute(fb_ctx* ctx, fb_bases* b, int window_bits);
 int fb_bases_get(fb_ctx* ctx, const fb_bases* b, uint64_t index, uint8_t out48[48]);
+/* window bits / number of windows of the set's table as built (0, 0: none) */
+int fb_bases_get_window(fb_ctx* ctx, const fb_bases* b, int* window_bits, int* num_windows);
 void fb_bases_free(fb_ctx* ctx, fb_bases* b);
 /* replaces g1_linear_combination on arbitrary points: out = sum_k s_k * P_k */
 int fb_msm(fb_ctx* ctx, const fb_bases* b, const uint8_t* scalars_be, uint64_t count, uint8_t out48[48]);
@@ -176,6 +215,13 @@ int fb_dev_worker_commit_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_f
 int fb_dev_worker_open_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
                                void* d_out128);
 
+/* fused commit + open: d_out = 48 bytes commitment | 32 bytes y | 48 bytes proof */
+int fb_dev_worker_commit_open(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len, const void* d_alpha_fr,
+                              void* d_out128);
+/* column shard: d_out = 96 bytes partial commitment | 32 bytes y | 96 bytes partial proof */
+int fb_dev_worker_commit_open_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len,
+                                      const void* d_alpha_fr, void* d_out224);
+
 /* uncompressed (96-byte) result, for the partial sums of an MSM sharded by point ranges */
 int fb_dev_msm_partial(fb_ctx* ctx, const fb_bases* b, const void* d_scalars_fr, uint64_t count, void* d_out96);
 /* batched rows (the bivariate row loop of src/bipoly.rs / benches/piano.rs:41-63), operands
@@ -191,6 +237,10 @@ uint64_t fb_launch_count(const fb_ctx* ctx);
  * writes a JSON object {"phase": [total_ms, count], ...} and resets the log */
 int fb_prof_enable(fb_ctx* ctx, int on);
 int fb_prof_read(fb_ctx* ctx, char* buf, size_t cap);
+/* work counters of the MSMs run while profiling was on (summed over lanes, reset by the read): out[0] MSMs,
+ * [1] sorted (point, window) entries, [2] output slots of the batched-affine rounds, [3] survivors added by the
+ * XYZZ kernel, [4] buckets.  bench.py turns them into the number of Fp multiplications actually issued. */
+int fb_msm_stats(fb_ctx* ctx, uint64_t out[8]);
 
 #ifdef __cplusplus
 }
