@@ -306,13 +306,17 @@ def _backend(args):
     return PianoBackend(args.scale, args.machines_scale, device=args.device)
 
 
-def cmd_run(args) -> int:
-    be = _backend(args)
+def cmd_run(args, backend_factory=None) -> int:
+    # bind first: the reference client pings one second after spawning the process (fourier.py:113-122, 262-267);
+    # a connection made while the setup is still loading waits in the listen queue instead of being refused
+    handler = RpcHandler(None)
+    srv = make_server(handler, args.host, args.port)
+    be = (backend_factory or _backend)(args)
     if args.setup_path:  # omitted: generate a fresh setup (cli.rs:19-21, piano.rs:93-97)
         be.load_setup_from_file(args.setup_path, not args.uncompressed)
     else:
         be.setup(secrets.token_bytes(32), secrets.token_bytes(32))
-    srv = make_server(RpcHandler(be), args.host, args.port)
+    handler.backend = be
     print("fourier_b200 rpc listening on %s:%d (scale %d, machines_scale %d)"
           % (args.host, args.port, args.scale, args.machines_scale), flush=True)
     try:
@@ -325,15 +329,28 @@ def cmd_run(args) -> int:
     return 0
 
 
-def cmd_setup(args) -> int:
-    def refuse(path):
-        print("File %s already exists, use --overwrite to overwrite" % path, file=sys.stderr)
-        return 1
+def can_proceed(args) -> bool:
+    """SetupArgs::can_proceed (cli.rs:89-121): same checks, same order, same messages."""
+    def error(msg):
+        print(msg, file=sys.stderr)
+        return False
 
-    if os.path.exists(args.setup_path) and args.generate_setup and not args.overwrite:  # cli.rs:91-100
-        return refuse(args.setup_path)
+    if os.path.exists(args.setup_path) and args.generate_setup and not args.overwrite:
+        return error("File %s already exists, use --overwrite to overwrite" % args.setup_path)
     if os.path.exists(args.precompute_path) and args.generate_precompute and not args.overwrite:
-        return refuse(args.precompute_path)
+        return error("File %s already exists, use --overwrite to overwrite" % args.precompute_path)
+    if args.compress_existing and args.decompress_existing:
+        return error("Cannot compress and decompress at the same time, choose one")
+    if args.compress_existing and not args.uncompressed:
+        return error("Cannot compress an already compressed file")
+    if args.decompress_existing and args.uncompressed:
+        return error("Cannot decompress an already decompressed file")
+    return True
+
+
+def cmd_setup(args) -> int:
+    if not can_proceed(args):  # main.rs:13 asserts it: a refused combination ends the process with a failure
+        return 1
     be = _backend(args)
     compressed = not args.uncompressed
     if args.compress_existing or args.decompress_existing:  # re-encode an existing file
@@ -352,9 +369,9 @@ def cmd_setup(args) -> int:
     return 0
 
 
-def main(argv=None) -> int:
+def main(argv=None, backend_factory=None) -> int:
     args = _parser().parse_args(argv)
-    return cmd_run(args) if args.subcmd == "run" else cmd_setup(args)
+    return cmd_run(args, backend_factory) if args.subcmd == "run" else cmd_setup(args)
 
 
 if __name__ == "__main__":

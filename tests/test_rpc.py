@@ -173,6 +173,26 @@ def test_cli_flags_parse_like_the_reference():
     assert s.setup_path == "data/setup" and s.precompute_path == "data/precompute" and s.generate_setup and s.overwrite
 
 
+def test_setup_flag_combinations_are_refused_like_the_reference(tmp_path, capsys):
+    """SetupArgs::can_proceed (cli.rs:89-121), checked ahead of backend creation (no GPU needed to be refused)."""
+    existing = tmp_path / "setup"
+    existing.write_bytes(b"x")
+    base = ["setup", "--setup-path", str(existing), "--precompute-path", str(tmp_path / "pre"), "--scale", "4", "--machines-scale", "1"]
+    cases = [
+        (["--generate-setup"], "already exists, use --overwrite to overwrite"),
+        (["--compress-existing", "--decompress-existing", "--uncompressed"], "Cannot compress and decompress at the same time, choose one"),
+        (["--compress-existing"], "Cannot compress an already compressed file"),
+        (["--decompress-existing", "--uncompressed"], "Cannot decompress an already decompressed file"),
+    ]
+    for flags, msg in cases:
+        assert rpc.main(base + flags) == 1
+        assert msg in capsys.readouterr().err
+    pre = tmp_path / "pre"
+    pre.write_bytes(b"x")
+    assert rpc.main(["setup", "--setup-path", str(tmp_path / "new"), "--precompute-path", str(pre), "--generate-precompute"]) == 1
+    assert "already exists" in capsys.readouterr().err
+
+
 @pytest.mark.gpu
 def test_client_routine_over_http_on_gpu(gpu, tmp_path):
     """fourier.py:472-533 test_routine: setup file -> server -> random poly -> every
