@@ -221,6 +221,7 @@ def run_msm(args, env=None, emit=True):
     t0 = time.time()
     bases = be.bases_from_scalars(synth.fr_bytes(21, per, start))  # P_k = s_k * G
     bases.precompute(int(os.environ.get("FB_BENCH_WINDOW", "0")))
+    be.set_msm_split(int(os.environ.get("FB_BENCH_SPLIT", "1")))
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     h_scalars = torch.from_numpy(synth.fr_bytes(22, per, start).reshape(-1)).pin_memory()
@@ -299,7 +300,7 @@ def run_msm(args, env=None, emit=True):
             "config": {"workload": "one G1 MSM of 2^%d points P_k = s_k*G with random 255-bit scalars (BASELINE config 4)" % lg,
                        "parallelism": "1 GPU" if world == 1 else "point ranges over %d GPUs + all-gather of 96-byte partial sums" % world,
                        "l2": "inputs larger than L2 (window tables + scalars)", "setup_s": round(setup_s, 2),
-                       "window_bits": wbits, "windows": nwin},
+                       "window_bits": wbits, "windows": nwin, "msm_split": int(os.environ.get("FB_BENCH_SPLIT", "1"))},
             "e2e": {"value": n / (ms_e2e * 1e-3) / 1e6, "unit": "Mpts/s", "h2d_bytes_per_step": per * 32,
                     "d2h_bytes_per_step": 96 + (world * 96 if world > 1 else 0)},
             "gpu_launches": int(launches), "clocks": clk,
@@ -362,6 +363,7 @@ def run_bipoly(args, env=None, emit=True):
     gathered = torch.zeros(world * rows * 128, dtype=torch.uint8, device=dev) if world > 1 else None
 
     be.set_lanes(int(os.environ.get("FB_BENCH_LANES", "1")))
+    be.set_msm_split(int(os.environ.get("FB_BENCH_SPLIT", "1")))
 
     def step_device():
         be.dev_commit_rows(row0, rows, d_coeffs, T, d_c)
@@ -446,7 +448,7 @@ def run_bipoly(args, env=None, emit=True):
                                       "128 bytes per row, master step on rank 0" % (world, rows),
                        "l2": "inputs larger than L2 (window tables of the local rows + coefficient matrix)",
                        "srs_setup_s": round(setup_s, 2), "window_bits": wbits, "windows": nwin,
-                       "lanes": int(os.environ.get("FB_BENCH_LANES", "1"))},
+                       "lanes": int(os.environ.get("FB_BENCH_LANES", "1")), "msm_split": int(os.environ.get("FB_BENCH_SPLIT", "1"))},
             "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * rows * T * 32 + 32,
                     "d2h_bytes_per_step": rows * 128 + (world * rows * 128 if world > 1 else 0) + 128,
                     "includes": "master_commit + master_open on rank 0"},

@@ -26,6 +26,7 @@ SYMBOLS = [
     ("fb_ctx_get_window", C.c_int, [_ctx, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("fb_ctx_set_open_mode", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_set_staging", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_set_msm_split", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_set_lanes", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_join", C.c_int, [_ctx]),
     ("fb_srs_generate", C.c_int, [_ctx, _u8p, _u8p, C.c_uint64, C.c_uint64]),

@@ -25,6 +25,11 @@ static fb_lane* lane_create(int index, bool own_stream) {
         FB_CUDA(cudaStreamCreateWithFlags(&L->own_stream, cudaStreamNonBlocking));
         L->stream = L->own_stream;
     }
+    for (int k = 0; k < kMaxSplit - 1; k++) {
+        FB_CUDA(cudaStreamCreateWithFlags(&L->sub_stream[k], cudaStreamNonBlocking));
+        FB_CUDA(cudaEventCreateWithFlags(&L->sub_join[k], cudaEventDisableTiming));
+    }
+    FB_CUDA(cudaEventCreateWithFlags(&L->sub_fork, cudaEventDisableTiming));
     FB_CUDA(cudaEventCreateWithFlags(&L->ev_fork, cudaEventDisableTiming));
     FB_CUDA(cudaEventCreateWithFlags(&L->ev_done, cudaEventDisableTiming));
     FB_CUDA(cudaMalloc(&L->d_err, 2 * sizeof(int)));
@@ -41,6 +46,16 @@ static void lane_destroy(fb_lane* L) {
                       &L->msm.where, &L->msm.stage, &L->msm.inv, &L->msm.stats, &L->in_bytes, &L->fr_a, &L->fr_b, &L->fr_c,
                       &L->pt_a, &L->pt_b, &L->out_bytes, &L->scan, &L->small, &L->eng_a, &L->eng_b};
     for (DevBuf* b : bufs) b->release();
+    for (int k = 0; k < kMaxSplit - 1; k++) {
+        MsmScratch& s = L->msm_sub[k];
+        DevBuf* sb[] = {&s.counts, &s.offsets, &s.cursor, &s.sorted, &s.buckets, &s.block_sums, &s.seg_a, &s.seg_t, &s.order,
+                        &s.misc, &s.pts_a, &s.pts_b, &s.pref, &s.where, &s.stage, &s.inv, &s.stats};
+        for (DevBuf* b : sb) b->release();
+        if (L->sub_stream[k]) cudaStreamDestroy(L->sub_stream[k]);
+        if (L->sub_join[k]) cudaEventDestroy(L->sub_join[k]);
+    }
+    L->msm_parts.release();
+    if (L->sub_fork) cudaEventDestroy(L->sub_fork);
     for (auto& kv : L->prof.marks) cudaEventDestroy(kv.second);
     for (auto e : L->prof.pool) cudaEventDestroy(e);
     if (L->d_err) cudaFree(L->d_err);
@@ -149,6 +164,27 @@ void lane_h2d(fb_ctx* c, fb_lane* L, void* d_dst, const void* h_src, size_t byte
         FB_CUDA(cudaEventRecord(L->ev_stage[k], L->stream));
         off += cnt;
     }
+}
+
+void lane_msm(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, G1Xyzz* d_out,
+              const Fr* d_scalars2) {
+    const int S = (g_prof && g_prof->on) ? 1 : c->msm_split;  // per-phase timing needs one stream
+    if (S <= 1) {
+        msm_run(bases, d_scalars, len, batch, true, d_out, L->msm, L->stream, d_scalars2);
+        return;
+    }
+    MsmExec ex;
+    ex.S = S;
+    ex.scratch[0] = &L->msm;
+    ex.stream[0] = L->stream;
+    for (int k = 1; k < kMaxSplit; k++) {
+        ex.scratch[k] = &L->msm_sub[k - 1];
+        ex.stream[k] = L->sub_stream[k - 1];
+        ex.join[k] = L->sub_join[k - 1];
+    }
+    ex.fork = L->sub_fork;
+    ex.parts = &L->msm_parts;
+    msm_run_split(bases, d_scalars, len, batch, true, d_out, ex, d_scalars2);
 }
 
 const NttTables& ctx_ntt_tables(fb_ctx* c, fb_lane* L, int log_n) {
@@ -326,6 +362,13 @@ int fb_ctx_set_open_mode(fb_ctx* c, int mode) {
     return FB_OK;
 }
 
+int fb_ctx_set_msm_split(fb_ctx* c, int parts) {
+    if (!c || parts < 1 || parts > kMaxSplit) return FB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->msm_split = parts;
+    return FB_OK;
+}
+
 int fb_ctx_set_staging(fb_ctx* c, int mode) {
     if (!c || mode < 0 || mode > 1) return FB_ERR_ARG;
     std::lock_guard<std::mutex> lk(c->mu);
@@ -390,7 +433,7 @@ int fb_msm_stats(fb_ctx* c, uint64_t out[8]) {
         for (int i = 0; i < 8; i++) out[i] = 0;
         for (int k = 0; k <= kMaxLanes; k++) {
             fb_lane* L = all_lane(c, k);
-            if (!L->msm.stats_zeroed) continue;
+            if (!L->msm.stats_zeroed) continue;  // (profiling runs unsplit: the sub-MSM scratch never counts)
             unsigned long long h[8];
             FB_CUDA(cudaMemcpy(h, L->msm.stats.p, sizeof h, cudaMemcpyDeviceToHost));
             FB_CUDA(cudaMemset(L->msm.stats.p, 0, sizeof h));
@@ -543,7 +586,7 @@ static int msm_host(fb_ctx* c, fb_lane* L, const fb_bases* b, const uint8_t* sca
     ctx_reset_err(c, L);
     Fr* d_s = ctx_upload_fr(c, L, L->in_bytes, L->fr_a, scalars_be, count);
     G1Xyzz* d_r = L->small.as<G1Xyzz>(2);
-    msm_run(b->b, d_s, count, 1, true, d_r, L->msm, L->stream);
+    lane_msm(c, L, b->b, d_s, count, 1, d_r);
     uint8_t* d_ob = L->out_bytes.as<uint8_t>(96);
     G1Affine* aff = L->pt_b.as<G1Affine>(2);
     g1_xyzz_to_affine_batch(d_r, aff, 1, L->stream);
@@ -607,7 +650,7 @@ int fb_dev_msm(fb_ctx* c, const fb_bases* b, const void* d_scalars, uint64_t cou
     return ctx_call(c, FB_CALL_ASYNC, [&](fb_lane* L) -> int {
         if (!b || count > b->b.n) return ctx_fail(c, FB_ERR_ARG, "scalar count exceeds the base set");
         G1Xyzz* d_r = L->small.as<G1Xyzz>(2);
-        msm_run(b->b, (const Fr*)d_scalars, count, 1, true, d_r, L->msm, L->stream);
+        lane_msm(c, L, b->b, (const Fr*)d_scalars, count, 1, d_r);
         ctx_points_out(c, L, d_r, 1, (uint8_t*)d_out48);
         return FB_OK;
     });
@@ -616,7 +659,7 @@ int fb_dev_msm_partial(fb_ctx* c, const fb_bases* b, const void* d_scalars, uint
     return ctx_call(c, FB_CALL_ASYNC, [&](fb_lane* L) -> int {
         if (!b || count > b->b.n) return ctx_fail(c, FB_ERR_ARG, "scalar count exceeds the base set");
         G1Xyzz* d_r = L->small.as<G1Xyzz>(2);
-        msm_run(b->b, (const Fr*)d_scalars, count, 1, true, d_r, L->msm, L->stream);
+        lane_msm(c, L, b->b, (const Fr*)d_scalars, count, 1, d_r);
         G1Affine* aff = L->pt_b.as<G1Affine>(2);
         prof_mark("out.affine_compress", L->stream);
         g1_xyzz_to_affine_batch(d_r, aff, 1, L->stream);

@@ -26,8 +26,21 @@ template <class P, int NW>
 __device__ __forceinline__ void tree_inverse(Fe<P>* v) {
     if constexpr (NW == 1) {
         v[0] = fe_inv_gcd<P>(v[0]);
+    } else if constexpr (NW % 2 != 0 || (NW & (NW - 1)) != 0) {
+        // any count: running products up, one inversion, peel back (3(NW-1) dependent multiplies)
+        Fe<P> pre[NW];
+        pre[0] = v[0];
+#pragma unroll
+        for (int i = 1; i < NW; i++) pre[i] = fe_mul<P>(pre[i - 1], v[i]);
+        Fe<P> inv = fe_inv_gcd<P>(pre[NW - 1]);
+#pragma unroll
+        for (int i = NW - 1; i >= 1; i--) {
+            const Fe<P> vi = fe_mul<P>(inv, pre[i - 1]);
+            inv = fe_mul<P>(inv, v[i]);
+            v[i] = vi;
+        }
+        v[0] = inv;
     } else {
-        static_assert(NW % 2 == 0, "power-of-two warp count expected");
         Fe<P> prod[NW / 2];
 #pragma unroll
         for (int i = 0; i < NW / 2; i++) prod[i] = fe_mul<P>(v[2 * i], v[2 * i + 1]);

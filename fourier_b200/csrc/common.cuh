@@ -157,6 +157,21 @@ struct MsmScratch {
 // and the opening proof of one row in one pass (sort bookkeeping, rounds, reduction and their latency-bound tails once).
 void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
              MsmScratch& s, cudaStream_t st, const Fr* d_scalars2 = nullptr);
+// One MSM as S independent sub-MSMs on S streams: over point (column) ranges when there is one output (or the
+// shared-bases pair), over row ranges when the batch has many rows.  A sub-MSM's latency-bound phases (sort
+// bookkeeping, the gather-bound first pass, the per-launch inversion, the reduction tail) then run under another's
+// multiplier-bound ones.  stream[0] is the caller's stream; the others fork from it and join it again.
+constexpr int kMaxSplit = 4;
+struct MsmExec {
+    int S = 1;
+    MsmScratch* scratch[kMaxSplit] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t stream[kMaxSplit] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t fork = nullptr;
+    cudaEvent_t join[kMaxSplit] = {nullptr, nullptr, nullptr, nullptr};
+    DevBuf* parts = nullptr;  // S x 2 XYZZ partial sums (column split)
+};
+void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
+                   MsmExec& ex, const Fr* d_scalars2 = nullptr);
 // table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin, kTableStride bytes per entry
 void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, void* d_out, DevBuf& scratch,
                      cudaStream_t st);

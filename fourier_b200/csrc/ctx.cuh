@@ -38,6 +38,12 @@ struct fb_lane {
     bool busy = false;   // a host thread is inside a call on this lane
     bool dirty = false;  // asynchronous work enqueued since the last join
     fb::MsmScratch msm;
+    // sub-MSMs of a split MSM (msm_run_split): sub-job 0 uses `msm` on `stream`, the others these
+    fb::MsmScratch msm_sub[fb::kMaxSplit - 1];
+    cudaStream_t sub_stream[fb::kMaxSplit - 1] = {nullptr, nullptr, nullptr};
+    cudaEvent_t sub_fork = nullptr;
+    cudaEvent_t sub_join[fb::kMaxSplit - 1] = {nullptr, nullptr, nullptr};
+    fb::DevBuf msm_parts;
     fb::DevBuf in_bytes, fr_a, fr_b, fr_c, pt_a, pt_b, out_bytes, scan, small, eng_a, eng_b;
     fb::Prof prof;
     int* d_err = nullptr;
@@ -69,6 +75,7 @@ struct fb_ctx {
     bool excl = false;
     int window_pref = 0;
     int open_mode = 0;    // 0: evaluation form (default); 1: the reference's literal iNTT -> eval -> divide -> NTT
+    int msm_split = 1;    // sub-MSMs per MSM (fb_ctx_set_msm_split)
     int staging = 0;      // 0: pinned ring for pageable host input; 1: hand pageable pointers to cudaMemcpyAsync
 
     std::mutex tab_mu;  // twiddle tables are built on first use, by whichever lane needs them
@@ -103,6 +110,9 @@ fb_lane* ctx_acquire(fb_ctx* c, fb_call_kind kind);
 void ctx_release(fb_ctx* c, fb_lane* L, fb_call_kind kind);
 // host -> device copy on the lane's stream; pageable sources go through the lane's pinned ring
 void lane_h2d(fb_ctx* c, fb_lane* L, void* d_dst, const void* h_src, size_t bytes);
+// msm_run on the lane, split into the context's number of sub-MSMs when the job is large enough
+void lane_msm(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, G1Xyzz* d_out,
+              const Fr* d_scalars2 = nullptr);
 
 // run f(lane), mapping exceptions to status codes
 template <class F>

@@ -100,7 +100,7 @@ int need_full_cols(fb_ctx* c) {
 void row_msm(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_scalars, size_t len, G1Xyzz* d_out) {
     size_t lo = c->col0 < len ? c->col0 : len;
     size_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
-    msm_run(row_bases(c, i), d_scalars + lo, hi - lo, 1, true, d_out, L->msm, L->stream);
+    lane_msm(c, L, row_bases(c, i), d_scalars + lo, hi - lo, 1, d_out);
 }
 
 // the field half of worker_open on device for `batch` rows at once: d_coeffs (Montgomery,
@@ -354,7 +354,7 @@ int fb_commit_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coef
         ctx_reset_err(c, L);
         Fr* d_s = ctx_upload_fr(c, L, L->in_bytes, L->fr_a, coeffs_be, nrows * len);
         G1Xyzz* d_r = L->small.as<G1Xyzz>(nrows + 1);
-        msm_run(row_bases(c, row0), d_s, len, nrows, true, d_r, L->msm, L->stream);  // piano.rs:150-158
+        lane_msm(c, L, row_bases(c, row0), d_s, len, nrows, d_r);  // piano.rs:150-158
         uint8_t* d_ob = L->out_bytes.as<uint8_t>(48 * nrows);
         ctx_points_out(c, L, d_r, nrows, d_ob);
         FB_CUDA(cudaMemcpyAsync(out48s, d_ob, 48 * nrows, cudaMemcpyDeviceToHost, L->stream));
@@ -391,7 +391,7 @@ int fb_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs
         for (uint64_t r = 0; r < nrows; r += slab) {
             const uint64_t rc2 = nrows - r < slab ? nrows - r : slab;
             Fr* d_qhat = open_scalars(c, L, tab, d_all + r * len, len, d_alpha, d_ys + r, rc2);
-            msm_run(row_bases(c, row0 + r), d_qhat, len, rc2, true, d_r + r, L->msm, L->stream);  // piano.rs:228-236
+            lane_msm(c, L, row_bases(c, row0 + r), d_qhat, len, rc2, d_r + r);  // piano.rs:228-236
         }
         uint8_t* d_ob = L->out_bytes.as<uint8_t>(80 * nrows);
         ctx_points_out(c, L, d_r, nrows, d_ob + 32 * nrows);
@@ -508,7 +508,7 @@ int fb_dev_commit_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const void* d_c
         if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "more coefficients than columns");
         if (nrows == 0) return FB_OK;
         G1Xyzz* d_r = (G1Xyzz*)L->eng_b.get((nrows + 1) * sizeof(G1Xyzz));
-        msm_run(row_bases(c, row0), (const Fr*)d_coeffs, len, nrows, true, d_r, L->msm, L->stream);
+        lane_msm(c, L, row_bases(c, row0), (const Fr*)d_coeffs, len, nrows, d_r);
         ctx_points_out(c, L, d_r, nrows, (uint8_t*)d_out48s);
         return FB_OK;
     });
@@ -531,7 +531,7 @@ int fb_dev_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const void* d_coe
         for (uint64_t r = 0; r < nrows; r += slab) {
             const uint64_t rc2 = nrows - r < slab ? nrows - r : slab;
             Fr* d_qhat = open_scalars(c, L, tab, (const Fr*)d_coeffs + r * len, len, (const Fr*)d_alpha, d_ys + r, rc2);
-            msm_run(row_bases(c, row0 + r), d_qhat, len, rc2, true, d_r + r, L->msm, L->stream);
+            lane_msm(c, L, row_bases(c, row0 + r), d_qhat, len, rc2, d_r + r);
         }
         fr_to_be(d_ys, (uint8_t*)d_out_ys, nrows, L->stream);
         ctx_points_out(c, L, d_r, nrows, (uint8_t*)d_out_proofs);
@@ -629,7 +629,7 @@ static int dev_commit_open(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_coeffs
     G1Xyzz* d_r = L->small.as<G1Xyzz>(3);
     const size_t lo = c->col0 < len ? c->col0 : len;
     const size_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
-    msm_run(row_bases(c, i), d_coeffs + lo, hi - lo, 2, true, d_r, L->msm, L->stream, d_qhat + lo);  // piano.rs:150-158, 228-236
+    lane_msm(c, L, row_bases(c, i), d_coeffs + lo, hi - lo, 2, d_r, d_qhat + lo);  // piano.rs:150-158, 228-236
     fr_to_be(d_y, d_out + fmt, 1, L->stream);
     G1Affine* aff = L->pt_b.as<G1Affine>(3);
     prof_mark("out.affine_compress", L->stream);

@@ -333,8 +333,8 @@ __device__ __forceinline__ Fp slot_x_den(const char* pts, uint32_t stride, const
 // x coordinates only (pass 2 gathers the points itself).  Launched on pass 2's grid (the running
 // products are per thread), i.e. at 4 CTAs per SM: the loads of the next slot are issued before
 // the current product to keep two slots in flight per thread.
-template <int MODE>
-__global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) {
+template <int MODE, int NW>
+__device__ __forceinline__ void round_pass1_body(const RoundArgs& a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -367,13 +367,13 @@ __global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) {
         }
     }
     // one inversion per CTA (4 warps): 176 -> ~80 us per launch against one per warp (batchinv.cuh)
-    const Fp r = block_batch_inverse<F, 4>(run);
+    const Fp r = block_batch_inverse<F, NW>(run);
     if (active) a.inv[t] = r;
 }
 
 // MODE 0: streamed input; 1: the points parked by pass 1; 2: gather through the slot map
-template <int MODE>
-__global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
+template <int MODE, int NW>
+__device__ __forceinline__ void round_pass2_body(const RoundArgs& a) {
     using F = FpParams;
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -418,6 +418,17 @@ __global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) {
         st_affine(a.out + o, r);
     }
 }
+
+// CTA shapes of the round kernels: 4 warps x 4 CTAs/SM (124 registers; default) or 6 warps x 3 CTAs/SM at 112 registers
+// (18 instead of 16 warps per SM; FB_MSM_CTA=6)
+template <int MODE>
+__global__ void __launch_bounds__(128, 4) k_round_pass1(RoundArgs a) { round_pass1_body<MODE, 4>(a); }
+template <int MODE>
+__global__ void __launch_bounds__(128, 4) k_round_pass2(RoundArgs a) { round_pass2_body<MODE, 4>(a); }
+template <int MODE>
+__global__ void __maxnreg__(112) k_round_pass1_w6(RoundArgs a) { round_pass1_body<MODE, 6>(a); }
+template <int MODE>
+__global__ void __maxnreg__(112) k_round_pass2_w6(RoundArgs a) { round_pass2_body<MODE, 6>(a); }
 
 // work counters for the bench's real-multiply accounting (launched only while profiling is on)
 __global__ void k_stat_add(unsigned long long* stats, int slot, const uint32_t* __restrict__ val, unsigned long long add) {
@@ -714,6 +725,15 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
     }
 }
 
+// out[b] = sum_k parts[k * nout + b]
+__global__ void __launch_bounds__(32) k_sum_parts(const G1Xyzz* __restrict__ parts, int S, int nout, G1Xyzz* __restrict__ out) {
+    const int b = threadIdx.x;
+    if (b >= nout) return;
+    G1Xyzz acc = parts[b];
+    for (int k = 1; k < S; k++) g1_add(acc, parts[k * nout + b]);
+    out[b] = acc;
+}
+
 }  // namespace
 
 int msm_num_windows(int c) { return (255 + c - 1) / c; }  // scalars are recoded below 2^254 (k_digits)
@@ -788,13 +808,17 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
 
     // number of batched-affine rounds (0: gather + XYZZ only)
     const uint64_t entries = (uint64_t)n * nwin;
-    static int rounds_env = -2, round_blocks_per_sm = 0;
+    static int rounds_env = -2, round_blocks_per_sm = 0, round_warps = 4;
     if (rounds_env == -2) {
         const char* e = getenv("FB_MSM_ROUNDS");  // tuning knob: number of affine rounds (default: by size)
-        rounds_env = e ? atoi(e) : -1;
-        FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2<1>, 128, 0));
+        const char* w = getenv("FB_MSM_CTA");     // tuning knob: warps per CTA of the round kernels (4 or 6)
+        round_warps = (w && atoi(w) == 6) ? 6 : 4;
+        if (round_warps == 6) FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2_w6<1>, 192, 0));
+        else FB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&round_blocks_per_sm, k_round_pass2<1>, 128, 0));
         if (round_blocks_per_sm < 1) round_blocks_per_sm = 1;
+        rounds_env = e ? atoi(e) : -1;
     }
+    const uint32_t rthreads = 32u * (uint32_t)round_warps;
     // Measured on B200 (profiles/): three rounds ahead of the XYZZ kernel are ~8% faster than the
     // XYZZ kernel alone at 2^20 points (pass 2 runs at the multiplier's rate, pass 1 of the first
     // round is bound by the gather); small inputs do not amortise the per-round inversion.
@@ -862,10 +886,10 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         exclusive_scan(cnt_tmp, off_out, nbuckets + 1, s.block_sums, st);
         uint32_t blocks = (uint32_t)(kNumSMs * round_blocks_per_sm);
         {
-            uint64_t need = (ub_out / kMinSlots + 127) / 128 + 1;
+            uint64_t need = (ub_out / kMinSlots + rthreads - 1) / rthreads + 1;
             if (need < blocks) blocks = (uint32_t)need;
         }
-        const uint32_t rnt = blocks * 128;
+        const uint32_t rnt = blocks * rthreads;
         RoundArgs ra;
         ra.pts = pts_cur;
         ra.stride = stride_cur;
@@ -895,21 +919,21 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
             (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
             prof_mark("msm.round_pass1", st);
             if (regather) {
-                (++fb::g_launches, k_round_pass1<2><<<blocks, 128, 0, st>>>(ra));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<2><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<2><<<blocks, 128, 0, st>>>(ra)));
                 prof_mark("msm.round_pass2", st);
-                (++fb::g_launches, k_round_pass2<2><<<blocks, 128, 0, st>>>(ra));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<2><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<2><<<blocks, 128, 0, st>>>(ra)));
             } else {
                 ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
-                (++fb::g_launches, k_round_pass1<1><<<blocks, 128, 0, st>>>(ra));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<1><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<1><<<blocks, 128, 0, st>>>(ra)));
                 prof_mark("msm.round_pass2", st);
-                (++fb::g_launches, k_round_pass2<1><<<blocks, 128, 0, st>>>(ra));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<1><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<1><<<blocks, 128, 0, st>>>(ra)));
             }
         } else {
             (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
             prof_mark("msm.round_pass1", st);
-            (++fb::g_launches, k_round_pass1<0><<<blocks, 128, 0, st>>>(ra));
+            (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<0><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<0><<<blocks, 128, 0, st>>>(ra)));
             prof_mark("msm.round_pass2", st);
-            (++fb::g_launches, k_round_pass2<0><<<blocks, 128, 0, st>>>(ra));
+            (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<0><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<0><<<blocks, 128, 0, st>>>(ra)));
         }
         if (stats_on) k_stat_add<<<1, 1, 0, st>>>(stats, 2, off_out + nbuckets, 0);
         pts_cur = reinterpret_cast<const char*>(ra.out);
@@ -1006,6 +1030,53 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     (++fb::g_launches, k_bit_combine<<<nsets, 32, 0, st>>>(Q, k, tab ? d_out : S));
     if (!tab) (++fb::g_launches, k_window_combine<<<(unsigned)batch, 64, 0, st>>>(S, (uint32_t)nwin, c, d_out));
     prof_mark("post", st);
+    FB_CUDA(cudaGetLastError());
+}
+
+void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, bool scalars_mont, G1Xyzz* d_out,
+                   MsmExec& ex, const Fr* d_scalars2) {
+    const bool shared = d_scalars2 != nullptr;
+    const bool by_rows = !shared && batch >= 2;
+    int S = ex.S;
+    if (S > kMaxSplit) S = kMaxSplit;
+    // every sub-MSM keeps at least 2^17 points (columns) / 64 rows: below that the per-launch costs dominate
+    if (by_rows) {
+        while (S > 1 && batch / S < 64) S--;
+    } else {
+        while (S > 1 && len / S < ((size_t)1 << 17)) S--;
+    }
+    if (S <= 1) {
+        msm_run(bases, d_scalars, len, batch, scalars_mont, d_out, *ex.scratch[0], ex.stream[0], d_scalars2);
+        return;
+    }
+    cudaStream_t st0 = ex.stream[0];
+    FB_CUDA(cudaEventRecord(ex.fork, st0));
+    const size_t per_row = (size_t)(bases.c > 0 ? bases.nwin : 1) * bases.n;  // entries of one row of the (tabulated) bases
+    const int nout = shared ? 2 : 1;
+    G1Xyzz* parts = by_rows ? nullptr : ex.parts->as<G1Xyzz>((size_t)S * nout);
+    for (int k = 0; k < S; k++) {
+        cudaStream_t st = ex.stream[k];
+        if (k) FB_CUDA(cudaStreamWaitEvent(st, ex.fork, 0));
+        if (by_rows) {
+            const size_t r0 = batch * k / S, r1 = batch * (k + 1) / S;
+            MsmBases b = bases;
+            b.pts = (char*)bases.pts + r0 * per_row * bases.stride();
+            msm_run(b, d_scalars + r0 * len, len, r1 - r0, scalars_mont, d_out + r0, *ex.scratch[k], st);
+        } else {
+            const size_t c0 = len * k / S, c1 = len * (k + 1) / S;
+            MsmBases b = bases;
+            b.pts = (char*)bases.pts + c0 * bases.stride();  // index = w * bases.n + column: shifting the base shifts the column
+            b.n = bases.n;
+            // NB: msm_run checks len <= b.n against the (unshifted) row length, which still holds
+            msm_run(b, d_scalars + c0, c1 - c0, shared ? 2 : 1, scalars_mont, parts + (size_t)k * nout, *ex.scratch[k], st,
+                    shared ? d_scalars2 + c0 : nullptr);
+        }
+        if (k) {
+            FB_CUDA(cudaEventRecord(ex.join[k], st));
+            FB_CUDA(cudaStreamWaitEvent(st0, ex.join[k], 0));
+        }
+    }
+    if (!by_rows) (++fb::g_launches, k_sum_parts<<<1, 32, 0, st0>>>(parts, S, nout, d_out));
     FB_CUDA(cudaGetLastError());
 }
 

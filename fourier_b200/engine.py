@@ -148,6 +148,10 @@ class PianoBackend:
         """lanes >= 2: the heavy dev_* calls rotate over that many internal streams (overlap); see join()."""
         self._chk(self._lib.fb_ctx_set_lanes(self._ctx, lanes))
 
+    def set_msm_split(self, parts: int):
+        """parts >= 2: every large MSM runs as that many sub-MSMs on as many streams of its lane."""
+        self._chk(self._lib.fb_ctx_set_msm_split(self._ctx, parts))
+
     def join(self):
         """The caller's stream waits (on the device) for every dev_* call in flight on the lanes."""
         self._chk(self._lib.fb_ctx_join(self._ctx))

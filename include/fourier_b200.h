@@ -79,6 +79,10 @@ int fb_ctx_get_window(fb_ctx* ctx, int* window_bits, int* num_windows);
  * evaluations (no transform; identical field elements), 1 the reference's literal
  * sequence iNTT -> eval -> divide -> NTT (piano.rs:193-236).  Same bytes either way. */
 int fb_ctx_set_open_mode(fb_ctx* ctx, int mode);
+/* parts >= 2: every large MSM runs as `parts` independent sub-MSMs (point ranges, or row ranges of a batch) on
+ * `parts` streams of its lane, so that one sub-MSM's latency-bound phases run under another's multiplier-bound
+ * ones; the partial sums are added on the device.  Same bytes as parts = 1 (default). */
+int fb_ctx_set_msm_split(fb_ctx* ctx, int parts);
 /* uploads from PAGEABLE host memory (a Rust Vec<u8>, Python bytes): 0 (default) copy
  * through the lane's pinned double buffer, 1 hand the pointer to cudaMemcpyAsync.
  * Pinned / registered sources are always copied directly. */

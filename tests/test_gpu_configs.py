@@ -366,6 +366,31 @@ def test_lanes_overlap_device_calls_same_bytes(gpu):
     b.close()
 
 
+@pytest.mark.parametrize("n,m", [(19, 0), (14, 8)])
+def test_split_msm_same_bytes(gpu, n, m):
+    """fb_ctx_set_msm_split: one MSM as 2..4 sub-MSMs on sub-streams - over point ranges for a single row (and the
+    fused pair), over row ranges for a batch of rows - gives the bytes of the unsplit run."""
+    from fourier_b200 import PianoBackend, synth
+    M, T = 1 << m, 1 << (n - m)
+    b = PianoBackend(n, m)
+    b.setup(SECRET_X, SECRET_Y)
+    coeffs = synth.fr_bytes(91, M * T)
+    alpha_b = synth.fr_bytes(92, 1).tobytes()
+    want = (b.commit_rows(0, M, coeffs), b.open_rows(0, M, coeffs, alpha_b))
+    want_fused = b.worker_commit_open(M - 1, coeffs[(M - 1) * T:], alpha_b)
+    assert want_fused == (want[0][M - 1], want[1][0][M - 1], want[1][1][M - 1])
+    for parts in (2, 3, 4):
+        b.set_msm_split(parts)
+        for _ in range(2):
+            assert (b.commit_rows(0, M, coeffs), b.open_rows(0, M, coeffs, alpha_b)) == want
+            assert b.worker_commit_open(M - 1, coeffs[(M - 1) * T:], alpha_b) == want_fused
+    b.set_msm_split(1)
+    if m == 0:
+        o = known_tau_oracle(n, 0)
+        assert want[0][0] == bls.g1_compress(o.worker_commit_known_tau(0, synth.fr_ints(91, T)))
+    b.close()
+
+
 def test_pageable_and_pinned_host_inputs_agree(gpu):
     """A Rust Vec<u8> / Python bytes is pageable: it goes through the lane's pinned double buffer (several 4 MiB
     chunks here); a pinned tensor is copied directly; forcing the driver's own pageable path gives the same bytes."""
