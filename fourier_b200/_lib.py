@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfourier_b200.so")
+# FB_LIB_PATH: an alternative build of the same library (A/B runs of compile-time variants); never a fallback
+LIB_PATH = os.environ.get("FB_LIB_PATH") or os.path.join(_HERE, "libfourier_b200.so")
 
 # every symbol include/fourier_b200.h declares: (name, restype, argtypes)
 _u8p = C.c_void_p  # byte buffers are passed as addresses (bytes, bytearray, numpy, torch all work)

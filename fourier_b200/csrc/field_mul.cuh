@@ -164,8 +164,165 @@ FB_HD Fe<P> fe_mul(const Fe<P>& a, const Fe<P>& b) {
     return r;
 }
 
+// Montgomery step of a reduction-only row: like fe_mont_step, but limb 0 of the running value is Ev[0] + lone (the
+// limb that the division by 2^32 of the previous row left unpaired), and the carry of that addition enters the Od
+// chain at limb 1.  On return Ev[0] == 0 (mod 2^32) and the caller adds the final carry into Od[N-1].
 template <class P>
-FB_HD Fe<P> fe_sqr(const Fe<P>& a) { return fe_mul<P>(a, a); }
+FB_HD void fe_mont_step_lone(uint32_t* Ev, uint32_t* Od, uint32_t lone) {
+    constexpr int N = P::N;
+    if constexpr (P::INV == 0xffffffffu && P::mod(0) == 1u && P::mod(1) == 0xffffffffu) {
+        const uint32_t e0 = Ev[0] + lone;   // limb 0 (mod 2^32); the carry is regenerated right below
+        const uint32_t m = 0u - e0;
+        const uint32_t h1 = m - (m != 0u ? 1u : 0u);
+        Ev[0] = add_cc(Ev[0], lone);        // CF = carry into limb 1
+        Od[0] = addc_cc(e0, Od[0]);         // m*(2^32-1) = h1*2^32 + e0 at limbs (1, 2)
+        Od[1] = addc_cc(h1, Od[1]);
+#pragma unroll
+        for (int j = 3; j < N; j += 2) {
+            Od[j - 1] = madc_lo_cc(m, P::mod(j), Od[j - 1]);
+            Od[j] = (j == N - 1) ? madc_hi(m, P::mod(j), Od[j]) : madc_hi_cc(m, P::mod(j), Od[j]);
+        }
+        Ev[0] = add_cc(m, e0);              // = 0, carry 1 unless e0 == 0
+        Ev[1] = addc_cc(Ev[1], 0u);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            Ev[j] = madc_lo_cc(m, P::mod(j), Ev[j]);
+            Ev[j + 1] = madc_hi_cc(m, P::mod(j), Ev[j + 1]);
+        }
+    } else {
+        const uint32_t m = (Ev[0] + lone) * P::INV;
+        Ev[0] = add_cc(Ev[0], lone);
+        Od[0] = madc_lo_cc(m, P::mod(1), Od[0]);
+        Od[1] = madc_hi_cc(m, P::mod(1), Od[1]);
+#pragma unroll
+        for (int j = 3; j < N; j += 2) {
+            Od[j - 1] = madc_lo_cc(m, P::mod(j), Od[j - 1]);
+            Od[j] = (j == N - 1) ? madc_hi(m, P::mod(j), Od[j]) : madc_hi_cc(m, P::mod(j), Od[j]);
+        }
+        Ev[0] = mad_lo_cc(m, P::mod(0), Ev[0]);
+        Ev[1] = madc_hi_cc(m, P::mod(0), Ev[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            Ev[j] = madc_lo_cc(m, P::mod(j), Ev[j]);
+            Ev[j + 1] = madc_hi_cc(m, P::mod(j), Ev[j + 1]);
+        }
+    }
+}
+
+// Dedicated Montgomery squaring: N(N-1)/2 off-diagonal products (each once), doubled by a one-bit shift, the N
+// squares added by ONE carry chain, then a reduction of the low half only: N(N+1)/2 + N^2 wide MADs (Fp: 222
+// against the 288 of fe_mul; Fr: 92 against 112).
+//   1. off-diagonal sum D = sum_{i<j} a_i a_j 2^(32(i+j)): the product a_i*a_j occupies limbs (i+j, i+j+1), so the
+//      products of one row i with j-i odd tile the odd-aligned array Do from limb 2i+1 on, those with j-i even the
+//      even-aligned array De from limb 2i+2 on: two independent lo/hi carry chains per row, each closed by an
+//      addc into the limb above its top (which so far holds only such carries).
+//   2. S = 2(De + Do) + sum a_i^2 2^(64 i): one add chain, one funnel shift per limb, and the squares - they tile
+//      limbs (2i, 2i+1) - as one mad.lo.cc / madc.hi.cc chain whose addend is the shifted sum.
+//   3. REDC on the low half S_lo alone (the running value stays below 2^(32(N+1))), then + S_hi: with
+//      M = sum m_i 2^(32 i), (S_lo + M p) / R <= p and S_hi < p, so one final conditional subtraction.
+//      A reduction-only row is a Montgomery step plus the re-alignment of the two arrays after the division by
+//      2^32: the old odd-aligned array becomes the even-aligned one unchanged, the old even-aligned array minus
+//      its limbs 0 (now zero) and 1 becomes the odd-aligned one unchanged, and limb 1 - alone at the new limb
+//      0 - is carried into the next step (fe_mont_step_lone): no carry ripples between rows.
+template <class P>
+FB_HD Fe<P> fe_sqr(const Fe<P>& a) {
+#ifdef FB_SQR_VIA_MUL  // A/B builds only
+    return fe_mul<P>(a, a);
+#endif
+    constexpr int N = P::N;
+    static_assert(N % 2 == 0, "even limb count expected");
+    uint32_t De[2 * N + 2], Do[2 * N + 2];
+#pragma unroll
+    for (int i = 0; i < 2 * N + 2; i++) De[i] = Do[i] = 0;
+    // ---- 1. off-diagonal products
+#pragma unroll
+    for (int i = 0; i < N - 1; i++) {
+        // odd offsets j = i+1, i+3, ...: limbs 2i+1, ... of Do
+        {
+            bool first = true;
+            int top = 0;
+#pragma unroll
+            for (int j = i + 1; j < N; j += 2) {
+                const int k = i + j;
+                Do[k] = first ? mad_lo_cc(a.v[i], a.v[j], Do[k]) : madc_lo_cc(a.v[i], a.v[j], Do[k]);
+                Do[k + 1] = madc_hi_cc(a.v[i], a.v[j], Do[k + 1]);
+                first = false;
+                top = k + 1;
+            }
+            Do[top + 1] = addc(Do[top + 1], 0u);
+        }
+        // even offsets j = i+2, i+4, ...: limbs 2i+2, ... of De
+        if (i + 2 < N) {
+            bool first = true;
+            int top = 0;
+#pragma unroll
+            for (int j = i + 2; j < N; j += 2) {
+                const int k = i + j;
+                De[k] = first ? mad_lo_cc(a.v[i], a.v[j], De[k]) : madc_lo_cc(a.v[i], a.v[j], De[k]);
+                De[k + 1] = madc_hi_cc(a.v[i], a.v[j], De[k + 1]);
+                first = false;
+                top = k + 1;
+            }
+            De[top + 1] = addc(De[top + 1], 0u);
+        }
+    }
+    // ---- 2. S = 2 (De + Do) + squares
+    uint32_t T[2 * N];
+    T[0] = 0;  // no product reaches limb 0
+    T[1] = add_cc(De[1], Do[1]);
+#pragma unroll
+    for (int k = 2; k < 2 * N - 1; k++) T[k] = addc_cc(De[k], Do[k]);
+    T[2 * N - 1] = addc(De[2 * N - 1], Do[2 * N - 1]);
+    uint32_t S[2 * N];
+#pragma unroll
+    for (int k = 2 * N - 1; k >= 1; k--) T[k] = (T[k] << 1) | (T[k - 1] >> 31);  // D < 2^(64N-1): the top bit is free
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        S[2 * i] = (i == 0) ? mad_lo_cc(a.v[i], a.v[i], T[2 * i]) : madc_lo_cc(a.v[i], a.v[i], T[2 * i]);
+        S[2 * i + 1] = (i == N - 1) ? madc_hi(a.v[i], a.v[i], T[2 * i + 1]) : madc_hi_cc(a.v[i], a.v[i], T[2 * i + 1]);
+    }
+    // ---- 3. REDC of the low half
+    uint32_t buf0[N], buf1[N];
+    uint32_t* E = buf0;
+    uint32_t* O = buf1;
+#pragma unroll
+    for (int k = 0; k < N; k++) {
+        E[k] = S[k];
+        O[k] = 0;
+    }
+    fe_mont_step<P>(E, O);
+    O[N - 1] = addc(O[N - 1], 0);
+#pragma unroll
+    for (int i = 1; i < N; i++) {
+        // V / 2^32: the old O is the new even-aligned array; the old E from limb 2 on is the new odd-aligned one;
+        // the old E[1] stands alone at the new limb 0
+        uint32_t* nE = O;
+        uint32_t* nO = E;
+        const uint32_t lone = E[1];
+#pragma unroll
+        for (int k = 0; k < N - 2; k++) nO[k] = E[k + 2];
+        nO[N - 2] = 0;
+        nO[N - 1] = 0;
+        fe_mont_step_lone<P>(nE, nO, lone);
+        nO[N - 1] = addc(nO[N - 1], 0);
+        E = nE;
+        O = nO;
+    }
+    // ---- (E >> 32) + O + S_hi
+    uint32_t t[N];
+    t[0] = add_cc(O[0], E[1]);
+#pragma unroll
+    for (int k = 1; k < N - 1; k++) t[k] = addc_cc(O[k], E[k + 1]);
+    t[N - 1] = addc(O[N - 1], 0);
+    t[0] = add_cc(t[0], S[N]);
+#pragma unroll
+    for (int k = 1; k < N - 1; k++) t[k] = addc_cc(t[k], S[N + k]);
+    t[N - 1] = addc_cc(t[N - 1], S[2 * N - 1]);
+    const uint32_t top = addc(0, 0);
+    Fe<P> r;
+    fe_final_sub<P>(r.v, t, top);
+    return r;
+}
 
 // value -> Montgomery form and back
 template <class P>

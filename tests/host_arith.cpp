@@ -40,6 +40,18 @@ void h_fp_mul_portable(const uint32_t* a, const uint32_t* b, uint32_t* r) {
     Fp z = fe_mul_portable<FpParams>(x, y);
     memcpy(r, z.v, 48);
 }
+void h_fr_sqr(const uint32_t* a, uint32_t* r) {
+    Fr x;
+    memcpy(x.v, a, 32);
+    Fr z = fe_sqr<FrParams>(x);
+    memcpy(r, z.v, 32);
+}
+void h_fp_sqr(const uint32_t* a, uint32_t* r) {
+    Fp x;
+    memcpy(x.v, a, 48);
+    Fp z = fe_sqr<FpParams>(x);
+    memcpy(r, z.v, 48);
+}
 // op: 0 add, 1 sub, 2 neg(a), 3 inv(a), 4 to_mont(a), 5 from_mont(a), 6 inv_gcd(a)
 void h_fr_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
     Fr x, y, z;

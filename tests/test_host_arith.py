@@ -60,6 +60,16 @@ def test_field_ops(L, name, m, n):
         assert val(r) == (a - b) % m
         op(2, arr(a, n), arr(b, n), r)
         assert val(r) == (-a) % m
+    # dedicated Montgomery squaring (fe_sqr): every operand of the list above, plus limb patterns that drive the
+    # carries between the two product arrays and the lone-limb carry of the reduction rows
+    sqr = getattr(L, "h_%s_sqr" % name)
+    sq_cases = [a for a, _ in cases] + [b for _, b in cases]
+    sq_cases += [((1 << (32 * k)) - 1) % m for k in range(1, n + 1)] + [(m - (1 << (32 * k))) % m for k in range(n)]
+    sq_cases += [int("ffffffff00000000" * (n // 2), 16) % m, int("00000000ffffffff" * (n // 2), 16) % m,
+                 int("ffffffff" * n, 16) % m, int("80000000" * n, 16) % m, int("00000001" * n, 16) % m]
+    for a in sq_cases:
+        sqr(arr(a, n), r)
+        assert val(r) == a * a * Ri % m, hex(a)
     for a, b in cases[:30]:
         op(3, arr(a, n), arr(b, n), r)
         assert val(r) == (pow(a * Ri % m, -1, m) * RR % m if a else 0)
