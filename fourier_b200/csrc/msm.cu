@@ -38,8 +38,10 @@ struct DigitArgs {
     int mont;       // scalars are in Montgomery form
     int tabulated;  // single bucket set; entry = w*n + j
     uint32_t buckets_per_win;  // 2^(c-1) (index = |digit| - 1)
-    uint32_t* counts;   // histogram (pass 0) / cursors (pass 1)
+    uint32_t* counts;   // histogram (pass 0) / cursors (pass 1, 2)
     uint32_t* sorted;
+    const uint32_t* off_out;  // MODE 2: offsets of the first round's output slots (ceil(count / 2) per bucket)
+    uint32_t* where2;         // MODE 2: [slot][2] the slot's two table entries
 };
 
 __device__ __forceinline__ G1Affine ldg_affine(const G1Affine* p);
@@ -51,7 +53,9 @@ __device__ __forceinline__ void st_affine(G1Affine* dst, const G1Affine& r) {
     for (int i = 0; i < 3; i++) d[3 + i] = make_uint4(r.y.v[4 * i], r.y.v[4 * i + 1], r.y.v[4 * i + 2], r.y.v[4 * i + 3]);
 }
 
-// MODE 0: histogram of bucket sizes; 1: scatter (table index | sign) into bucket order.
+// MODE 0: histogram of bucket sizes; 1: scatter (table index | sign) into bucket order; 2: scatter straight into
+// the slot map of the first batched-affine round (the k-th entry of a bucket is input k & 1 of the bucket's output
+// slot k >> 1; cursors start at 0), which then needs neither the sorted list nor a slot-map kernel.
 // (Scattering the points themselves, so that later kernels stream instead of gather, was
 // measured: 1.5 ms of random 96-byte writes per 2^20 MSM, slower than the gathers it saves.)
 template <int MODE>
@@ -231,6 +235,28 @@ __global__ void __launch_bounds__(256) k_slot_map(const uint32_t* __restrict__ o
         if (GATHER) where2[o] = make_uint2(sorted[e], has2 ? sorted[e + 1] : kNone);
         else where[o] = e | (has2 ? 0x80000000u : 0u);
     }
+}
+
+// streamed rounds: one warp per bucket writes the bucket's slots (no search): slot i of bucket b adds the
+// inputs off_in[b] + 2i and + 2i + 1 (the last slot of an odd bucket has one input)
+__global__ void __launch_bounds__(256) k_slot_fill(const uint32_t* __restrict__ off_in, const uint32_t* __restrict__ off_out,
+                                                   uint32_t nbuckets, uint32_t* __restrict__ where) {
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < nbuckets; b += (gridDim.x * blockDim.x) >> 5) {
+        const uint32_t i0 = off_in[b], cnt = off_in[b + 1] - i0, o0 = off_out[b];
+        const uint32_t nout = (cnt + 1) >> 1;
+        for (uint32_t i = lane; i < nout; i += 32u) where[o0 + i] = (i0 + 2u * i) | ((2u * i + 1u < cnt) ? 0x80000000u : 0u);
+    }
+}
+
+// first round with the direct scatter (k_digits<2>): a bucket with an odd number of entries leaves the second
+// input of its last slot unwritten - mark it (runs BEFORE the scatter, which never writes that word)
+__global__ void __launch_bounds__(256) k_mark_single(const uint32_t* __restrict__ off_in, const uint32_t* __restrict__ off_out,
+                                                     uint32_t nbuckets, uint32_t* __restrict__ where2) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbuckets) return;
+    const uint32_t cnt = off_in[b + 1] - off_in[b];
+    if (cnt & 1u) where2[2u * (off_out[b + 1] - 1u) + 1u] = kNone;
 }
 
 template <bool GATHER>
@@ -725,12 +751,12 @@ __global__ void __launch_bounds__(128) k_build_table(const G1Affine* __restrict_
     }
 }
 
-// out[b] = sum_k parts[k * nout + b]
-__global__ void __launch_bounds__(32) k_sum_parts(const G1Xyzz* __restrict__ parts, int S, int nout, G1Xyzz* __restrict__ out) {
+// out[b] = sum_q parts[b * P + q]  (b < nout outputs, P partial sums each)
+__global__ void __launch_bounds__(32) k_sum_parts(const G1Xyzz* __restrict__ parts, int P, int nout, G1Xyzz* __restrict__ out) {
     const int b = threadIdx.x;
     if (b >= nout) return;
-    G1Xyzz acc = parts[b];
-    for (int k = 1; k < S; k++) g1_add(acc, parts[k * nout + b]);
+    G1Xyzz acc = parts[b * P];
+    for (int q = 1; q < P; q++) g1_add(acc, parts[b * P + q]);
     out[b] = acc;
 }
 
@@ -856,10 +882,34 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     (++fb::g_launches, k_digits<0><<<gb, 256, 0, st>>>(a));
     prof_mark("msm.scan", st);
     exclusive_scan(counts, offsets, nbuckets + 1, s.block_sums, st);
-    FB_CUDA(cudaMemcpyAsync(cursor, offsets, nbuckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     a2.counts = cursor;
-    prof_mark("msm.scatter", st);
-    (++fb::g_launches, k_digits<1><<<gb, 256, 0, st>>>(a2));
+    // With batched-affine rounds the scatter writes the first round's slot map directly (k_digits<2>): the output
+    // offsets of that round (ceil(count / 2) per bucket, scanned) are formed first, into `counts` (the histogram has
+    // been consumed by the scan).  FB_MSM_DIRECT=0 keeps the sorted list + slot-map kernel.
+    static int direct_env = -1;
+    if (direct_env < 0) {
+        const char* e = getenv("FB_MSM_DIRECT");
+        direct_env = e ? atoi(e) : 1;
+    }
+    const bool direct = rounds > 0 && direct_env != 0;
+    uint32_t* wbuf0 = nullptr;
+    if (direct) {
+        const uint64_t ub_out0 = (entries + nbuckets) / 2 + 1;
+        uint32_t* cnt_tmp = s.order.as<uint32_t>(nbuckets + 1);
+        (++fb::g_launches, k_halve_counts<<<(nbuckets + 256) / 256, 256, 0, st>>>(offsets, nbuckets, cnt_tmp));
+        exclusive_scan(cnt_tmp, counts, nbuckets + 1, s.block_sums, st);
+        wbuf0 = s.where.as<uint32_t>(2 * ub_out0);
+        (++fb::g_launches, k_mark_single<<<(nbuckets + 255) / 256, 256, 0, st>>>(offsets, counts, nbuckets, wbuf0));
+        FB_CUDA(cudaMemsetAsync(cursor, 0, nbuckets * sizeof(uint32_t), st));
+        a2.off_out = counts;
+        a2.where2 = wbuf0;
+        prof_mark("msm.scatter", st);
+        (++fb::g_launches, k_digits<2><<<gb, 256, 0, st>>>(a2));
+    } else {
+        FB_CUDA(cudaMemcpyAsync(cursor, offsets, nbuckets * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        prof_mark("msm.scatter", st);
+        (++fb::g_launches, k_digits<1><<<gb, 256, 0, st>>>(a2));
+    }
     const bool stats_on = g_prof && g_prof->on;
     unsigned long long* stats = s.stats.as<unsigned long long>(8);
     if (stats_on) {
@@ -880,10 +930,12 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     for (int r = 0; r < rounds; r++) {
         prof_mark("msm.round_map", st);
         const uint64_t ub_out = (ub + nbuckets) / 2 + 1;
-        uint32_t* cnt_tmp = s.order.as<uint32_t>(nbuckets + 1);
         uint32_t* off_out = (r & 1) ? cursor : counts;
-        (++fb::g_launches, k_halve_counts<<<(nbuckets + 256) / 256, 256, 0, st>>>(off_cur, nbuckets, cnt_tmp));
-        exclusive_scan(cnt_tmp, off_out, nbuckets + 1, s.block_sums, st);
+        if (!(direct && r == 0)) {  // (the direct scatter formed round 0's offsets already)
+            uint32_t* cnt_tmp = s.order.as<uint32_t>(nbuckets + 1);
+            (++fb::g_launches, k_halve_counts<<<(nbuckets + 256) / 256, 256, 0, st>>>(off_cur, nbuckets, cnt_tmp));
+            exclusive_scan(cnt_tmp, off_out, nbuckets + 1, s.block_sums, st);
+        }
         uint32_t blocks = (uint32_t)(kNumSMs * round_blocks_per_sm);
         {
             uint64_t need = (ub_out / kMinSlots + rthreads - 1) / rthreads + 1;
@@ -916,7 +968,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
                 const char* e = getenv("FB_MSM_REGATHER");
                 regather = e ? atoi(e) : 1;
             }
-            (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
+            if (!direct) (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
             prof_mark("msm.round_pass1", st);
             if (regather) {
                 (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<2><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<2><<<blocks, 128, 0, st>>>(ra)));
@@ -929,7 +981,11 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
                 (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<1><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<1><<<blocks, 128, 0, st>>>(ra)));
             }
         } else {
-            (++fb::g_launches, k_slot_map<false><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, nullptr, wbuf, nullptr));
+            {
+                uint32_t fb_blocks = (nbuckets + 7) / 8;  // 8 warps per CTA, one bucket per warp
+                if (fb_blocks > 16u * kNumSMs) fb_blocks = 16u * kNumSMs;
+                (++fb::g_launches, k_slot_fill<<<fb_blocks, 256, 0, st>>>(off_cur, off_out, nbuckets, wbuf));
+            }
             prof_mark("msm.round_pass1", st);
             (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<0><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<0><<<blocks, 128, 0, st>>>(ra)));
             prof_mark("msm.round_pass2", st);
@@ -1039,11 +1095,17 @@ void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_
     const bool by_rows = !shared && batch >= 2;
     int S = ex.S;
     if (S > kMaxSplit) S = kMaxSplit;
-    // every sub-MSM keeps at least 2^17 points (columns) / 64 rows: below that the per-launch costs dominate
+    // The shared-bases pair (commit + open of one row) splits into its two rows first - two plain MSMs over the same
+    // table on two streams - and only then into column halves.  Every sub-MSM keeps at least 2^17 points (columns) /
+    // 64 rows: below that the per-launch costs dominate.
+    int col_parts = shared ? S / 2 : S;  // column ranges per scalar vector
+    if (col_parts < 1) col_parts = 1;
     if (by_rows) {
         while (S > 1 && batch / S < 64) S--;
     } else {
-        while (S > 1 && len / S < ((size_t)1 << 17)) S--;
+        while (col_parts > 1 && len / col_parts < ((size_t)1 << 17)) col_parts--;
+        if (shared && len < ((size_t)1 << 17)) S = 1;       // small pair: one fused pass
+        else S = shared ? 2 * col_parts : col_parts;
     }
     if (S <= 1) {
         msm_run(bases, d_scalars, len, batch, scalars_mont, d_out, *ex.scratch[0], ex.stream[0], d_scalars2);
@@ -1053,7 +1115,8 @@ void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_
     FB_CUDA(cudaEventRecord(ex.fork, st0));
     const size_t per_row = (size_t)(bases.c > 0 ? bases.nwin : 1) * bases.n;  // entries of one row of the (tabulated) bases
     const int nout = shared ? 2 : 1;
-    G1Xyzz* parts = by_rows ? nullptr : ex.parts->as<G1Xyzz>((size_t)S * nout);
+    // column split: parts[k][b]; a sub-MSM of the pair writes one output (vector v, column range q: k = v * col_parts + q)
+    G1Xyzz* parts = by_rows ? nullptr : ex.parts->as<G1Xyzz>((size_t)S);
     for (int k = 0; k < S; k++) {
         cudaStream_t st = ex.stream[k];
         if (k) FB_CUDA(cudaStreamWaitEvent(st, ex.fork, 0));
@@ -1063,20 +1126,18 @@ void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_
             b.pts = (char*)bases.pts + r0 * per_row * bases.stride();
             msm_run(b, d_scalars + r0 * len, len, r1 - r0, scalars_mont, d_out + r0, *ex.scratch[k], st);
         } else {
-            const size_t c0 = len * k / S, c1 = len * (k + 1) / S;
+            const int v = k / col_parts, q = k % col_parts;
+            const size_t c0 = len * q / col_parts, c1 = len * (q + 1) / col_parts;
             MsmBases b = bases;
             b.pts = (char*)bases.pts + c0 * bases.stride();  // index = w * bases.n + column: shifting the base shifts the column
-            b.n = bases.n;
-            // NB: msm_run checks len <= b.n against the (unshifted) row length, which still holds
-            msm_run(b, d_scalars + c0, c1 - c0, shared ? 2 : 1, scalars_mont, parts + (size_t)k * nout, *ex.scratch[k], st,
-                    shared ? d_scalars2 + c0 : nullptr);
+            msm_run(b, (v ? d_scalars2 : d_scalars) + c0, c1 - c0, 1, scalars_mont, parts + k, *ex.scratch[k], st);
         }
         if (k) {
             FB_CUDA(cudaEventRecord(ex.join[k], st));
             FB_CUDA(cudaStreamWaitEvent(st0, ex.join[k], 0));
         }
     }
-    if (!by_rows) (++fb::g_launches, k_sum_parts<<<1, 32, 0, st0>>>(parts, S, nout, d_out));
+    if (!by_rows) (++fb::g_launches, k_sum_parts<<<1, 32, 0, st0>>>(parts, col_parts, nout, d_out));
     FB_CUDA(cudaGetLastError());
 }
 
