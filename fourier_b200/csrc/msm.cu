@@ -101,6 +101,11 @@ __global__ void __launch_bounds__(256) k_digits(DigitArgs a) {
         uint32_t bucket = (a.tabulated ? row : row * a.nwin + (uint32_t)w) * a.buckets_per_win + mag - 1;
         if (MODE == 0) {
             atomicAdd(a.counts + bucket, 1u);
+        } else if (MODE == 2) {
+            const uint32_t k = atomicAdd(a.counts + bucket, 1u);  // cursors start at 0: the entry's rank in its bucket
+            const uint32_t brow = row * a.row_bases;
+            const uint32_t idx = a.tabulated ? (brow * a.nwin + (uint32_t)w) * a.stride + col : brow * a.stride + col;
+            a.where2[2u * (a.off_out[bucket] + (k >> 1)) + (k & 1u)] = idx | ((neg ^ sneg) << 31);
         } else {
             uint32_t slot = atomicAdd(a.counts + bucket, 1u);
             const uint32_t brow = row * a.row_bases;
