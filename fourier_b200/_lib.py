@@ -75,6 +75,7 @@ SYMBOLS = [
     ("fb_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
     ("fb_dev_worker_commit_open", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     ("fb_dev_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    ("fb_dev_evaluate_noalloc", C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fb_launch_count", C.c_uint64, [_ctx]),
     ("fb_prof_enable", C.c_int, [_ctx, C.c_int]),
     ("fb_prof_read", C.c_int, [_ctx, C.c_char_p, C.c_size_t]),

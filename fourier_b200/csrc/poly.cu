@@ -8,7 +8,7 @@
 // quotient is q_k = s_(k+1).  On the GPU it runs as a blocked suffix scan: chunks
 // of L coefficients are collapsed to one value each (up-sweep, with multiplier
 // x^L), recursively, then the chunk boundary values are pushed back down.
-#include "common.cuh"
+#include "ctx.cuh"  // (common.cuh + the status codes of the C ABI, for fb_dev_evaluate_noalloc at the end)
 
 namespace fb {
 
@@ -222,3 +222,100 @@ void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, D
 }
 
 }  // namespace fb
+
+// ---------------------------------------------------------------------------------------------------------
+// fb_dev_evaluate_noalloc - FsPoly::eval for callers that cannot allocate (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels as horner_quotient's evaluation-only path (k_level_pows,
+// k_horner_up per level, k_horner_top, k_gather_first); the only difference is where the scratch lives:
+// a file-scope __device__ array instead of a grow-on-demand cudaMalloc'ed buffer.
+//
+//   * kNoAllocMaxLen = 2^20 coefficients.  Scratch = level powers + the collapsed levels
+//     (2^15 + 2^10 + 2^5 values) + the top level's suffix values, 33 920 Fr = 1.04 MiB, held by every GPU
+//     that loads the library until the process exits.
+//   * Every call shares the array and it keeps the last call's contents.  Nothing has to start at zero:
+//     every word a call reads was written earlier in the same call (level l's sz[l] values by k_horner_up,
+//     the top level's by k_horner_top), so stale data from a longer, earlier call is never read.
+//   * Calls that overlap on the GPU (two streams, two host threads) RACE on the array: serialise them.
+//   * The array's name is a host-side stand-in in host code, not a device address: the address is looked up
+//     once per device, with that device current, by cudaGetSymbolAddress, and that pointer goes to the kernels.
+//     The look-up happens on the first call for a device: make one call before starting a graph capture.
+namespace fb {
+namespace {
+
+constexpr uint64_t kNoAllocMaxLen = 1ull << 20;
+constexpr int kNoAllocMaxLevels = 4;  // 2^20 -> 2^15 -> 2^10 -> 2^5: three up-sweeps
+constexpr size_t kNoAllocScratchFr = (kNoAllocMaxLevels + 2) + ((1u << 15) + (1u << 10) + (1u << 5)) + kChunk + 58;  // 33 920
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchFr * sizeof(Fr)];
+
+constexpr int kNoAllocMaxDevices = 64;
+Fr* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+// device address of g_noalloc_scratch on `device` (which is current); nullptr + *err on failure
+Fr* noalloc_scratch_for(int device, cudaError_t* err) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        *err = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (*err != cudaSuccess) return nullptr;
+        g_noalloc_ptr[device] = static_cast<Fr*>(p);
+    }
+    return g_noalloc_ptr[device];
+}
+
+}  // namespace
+}  // namespace fb
+
+extern "C" int fb_dev_evaluate_noalloc(int device, const void* d_poly_fr, uint64_t len, const void* d_x_fr, void* d_out_y_fr,
+                                       void* cuda_stream) {
+    using namespace fb;
+    if (device < 0 || device >= kNoAllocMaxDevices) return ctx_fail(nullptr, FB_ERR_ARG, "fb_dev_evaluate_noalloc: device ordinal out of range");
+    if (!d_x_fr || !d_out_y_fr || (len && !d_poly_fr)) return ctx_fail(nullptr, FB_ERR_ARG, "fb_dev_evaluate_noalloc: null pointer");
+    if (len > kNoAllocMaxLen)
+        return ctx_fail(nullptr, FB_ERR_ARG, "fb_dev_evaluate_noalloc: more than 2^20 coefficients (the static scratch is sized for 2^20); use fb_evaluate");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return ctx_fail(nullptr, FB_ERR_CUDA, "fb_dev_evaluate_noalloc: cudaSetDevice failed");
+    }
+    Fr* base = noalloc_scratch_for(device, &e);
+    if (!base) {
+        cudaGetLastError();
+        return ctx_fail(nullptr, FB_ERR_CUDA, "fb_dev_evaluate_noalloc: cudaGetSymbolAddress failed");
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const Fr* d_a = static_cast<const Fr*>(d_poly_fr);
+    const Fr* d_x = static_cast<const Fr*>(d_x_fr);
+    Fr* d_y = static_cast<Fr*>(d_out_y_fr);
+    if (len == 0) {  // the empty polynomial evaluates to 0
+        e = cudaMemsetAsync(d_y, 0, sizeof(Fr), st);
+    } else {
+        size_t sz[kNoAllocMaxLevels + 1];
+        int levels = 0;
+        sz[0] = (size_t)len;
+        while (sz[levels] > (size_t)kChunk) {
+            sz[levels + 1] = (sz[levels] + kChunk - 1) >> kChunkLog;
+            levels++;
+        }
+        // layout: pows[levels + 2] | h_1 .. h_levels | s_top (<= kChunk values)
+        Fr* pows = base;
+        Fr* hp = base + (kNoAllocMaxLevels + 2);
+        (++fb::g_launches, k_level_pows<<<1, 1, 0, st>>>(d_x, pows, levels));
+        const Fr* cur = d_a;
+        for (int l = 1; l <= levels; l++) {
+            (++fb::g_launches, k_horner_up<<<dim3((unsigned)((sz[l] + 127) / 128), 1), 128, 0, st>>>(cur, sz[l - 1], pows + (l - 1), hp, sz[l]));
+            cur = hp;
+            hp += sz[l];
+        }
+        Fr* stop = hp;  // suffix values of the top level (sz[levels] <= kChunk of them)
+        (++fb::g_launches, k_horner_top<<<1, 64, 0, st>>>(cur, sz[levels], pows + levels, stop, 1));
+        (++fb::g_launches, k_gather_first<<<1, 64, 0, st>>>(stop, sz[levels], d_y, 1));
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return ctx_fail(nullptr, FB_ERR_CUDA, "fb_dev_evaluate_noalloc: kernel launch failed");
+    }
+    return FB_OK;
+}

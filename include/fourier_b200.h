@@ -235,6 +235,20 @@ int fb_dev_commit_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d
 int fb_dev_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d_coeffs_fr, uint64_t len,
                      const void* d_alpha_fr, void* d_out_ys_be, void* d_out_proof48s);
 
+/* ---- allocation-free evaluation ---------------------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  y = sum_k poly[k] x^k (FsPoly::eval) on operands already in HBM: d_poly_fr = len Montgomery
+ * Fr (as written by fb_dev_fr_from_be), d_x_fr and d_out_y_fr = one Montgomery Fr each.  Needs no
+ * context; asynchronous on `cuda_stream` (a cudaStream_t) of device `device`.  Calls no cudaMalloc /
+ * cudaFree: the scratch of the blocked Horner scan is a static __device__ array of 1.04 MiB that
+ * every GPU loading the library holds until exit, sized for len <= 2^20 (FB_ERR_ARG beyond that,
+ * message from fb_last_error(NULL)).  All calls share that array: calls that overlap on the GPU
+ * race, so serialise them (one stream, or events).  The first call on a device looks the array's
+ * address up (cudaGetSymbolAddress): make one call before beginning a graph capture. */
+int fb_dev_evaluate_noalloc(int device, const void* d_poly_fr, uint64_t len, const void* d_x_fr, void* d_out_y_fr,
+                            void* cuda_stream);
+
 /* number of kernel launches issued by this library so far */
 uint64_t fb_launch_count(const fb_ctx* ctx);
 /* per-phase device timing (CUDA events on the launching stream); fb_prof_read
