@@ -153,6 +153,11 @@ def own_arm(args):
     d_res = torch.zeros(2 * P + 32, dtype=torch.uint8, device=dev)
     d_open = torch.zeros(32 + P, dtype=torch.uint8, device=dev)
     gathered = torch.zeros(world * (2 * P + 32), dtype=torch.uint8, device=dev) if world > 1 else None
+    # N > 1, field half sharded too: this rank's slice of the coefficients, the 128-byte states of all ranks, the final record
+    d_slice = d_coeffs[col0 * 32:(col0 + ncols) * 32]
+    d_state = torch.zeros(128, dtype=torch.uint8, device=dev)
+    d_states = torch.zeros(world * 128, dtype=torch.uint8, device=dev)
+    d_final = torch.zeros(128, dtype=torch.uint8, device=dev)
 
     def step_separate():
         if world == 1:
@@ -168,27 +173,28 @@ def own_arm(args):
         else:
             be.dev_worker_commit_open_partial(0, d_coeffs, n, d_alpha, d_res)
 
+    def step_sharded():
+        """N > 1 only: every rank runs the field half over ITS slice; one all-gather of 128 bytes in the middle"""
+        be.dev_commit_open_shard_begin(0, d_slice, n, d_alpha, d_state)
+        dist.all_gather_into_tensor(d_states, d_state)
+        be.dev_commit_open_shard_finish(0, d_slice, n, d_alpha, d_states, world, d_res)
+
     def finish(separate):
-        """outputs ordered on the caller's stream; N > 1: the all-gather of the partial sums"""
+        """outputs ordered on the caller's stream; N > 1: the all-gather of the partials and their sum, on the device"""
         be.join()
         if separate:
             d_res[P:].copy_(d_open)
         if world > 1:
             dist.all_gather_into_tensor(gathered, d_res)
-
-    def combine(g: bytes):
-        w = 2 * P + 32
-        parts_c = [g[k * w:k * w + P] for k in range(world)]
-        parts_p = [g[k * w + P + 32:(k + 1) * w] for k in range(world)]
-        return be.g1_sum(b"".join(parts_c), fmt=96), g[P:P + 32], be.g1_sum(b"".join(parts_p), fmt=96)
+            be.dev_combine_commit_open(gathered, world, d_final)
 
     def result():
-        if world == 1:
-            r = bytes(d_res.cpu().numpy())
-            return r[:48], r[48:80], r[80:128]
-        return combine(bytes(gathered.cpu().numpy()))
+        r = bytes((d_res if world == 1 else d_final).cpu().numpy())
+        return r[:48], r[48:80], r[80:128]
 
     variants = {"separate": (1, step_separate, True), "overlap": (2, step_separate, True), "fused": (1, step_fused, False)}
+    if world > 1:
+        variants["sharded"] = (1, step_sharded, False)
     only = os.environ.get("FB_BENCH_STEP")  # measure one variant only (A/B runs, ncu)
     if only:
         variants = {only: variants[only]}
@@ -221,28 +227,41 @@ def own_arm(args):
     launches = launches_by[best]
 
     # ---- e2e: public host API, H2D + D2H inside the timed region
-    def host_step(fused, src):
+    h_slice = h_coeffs[col0 * 32:(col0 + ncols) * 32]  # (a view of the pinned buffer)
+
+    def host_step(kind, src):
         if world == 1:
-            if fused:
+            if kind == "fused":
                 return be.worker_commit_open(0, src, alpha_b)
             c = be.worker_commit(0, src)
             y, p = be.worker_open(0, src, alpha_b)
             return c, y, p
-        if fused:
+        if kind == "sharded":  # host slice up once, 128-byte states exchanged, partials gathered
+            st = be.commit_open_shard_begin(0, src, n, alpha_b)
+            mine = torch.frombuffer(bytearray(st), dtype=torch.uint8).to(dev)
+            dist.all_gather_into_tensor(d_states, mine)
+            c, y, p = be.commit_open_shard_finish(0, bytes(d_states.cpu().numpy()), alpha_b)
+        elif kind == "fused":
             c, y, p = be.worker_commit_open_partial(0, src, alpha_b)
         else:
             c = be.worker_commit_partial(0, src)
             y, p = be.worker_open_partial(0, src, alpha_b)
         mine = torch.frombuffer(bytearray(c + y + p), dtype=torch.uint8).to(dev)
         dist.all_gather_into_tensor(gathered, mine)
-        return combine(bytes(gathered.cpu().numpy()))
+        be.dev_combine_commit_open(gathered, world, d_final)
+        torch.cuda.current_stream().synchronize()
+        r = bytes(d_final.cpu().numpy())
+        return r[:48], r[48:80], r[80:128]
 
     pageable = coeffs_np.tobytes()  # a plain bytes object: what a Rust Vec<u8> / Python caller hands over
     e2e = {}
-    for name, fused, src in (("separate_pinned", False, h_coeffs), ("fused_pinned", True, h_coeffs),
-                             ("separate_pageable", False, pageable), ("fused_pageable", True, pageable),
-                             ("fused_pageable_driver_staged", True, pageable)):
-        if only and ("fused" in name) != (only == "fused"):
+    host_cases = [("separate_pinned", "separate", h_coeffs), ("fused_pinned", "fused", h_coeffs),
+                  ("separate_pageable", "separate", pageable), ("fused_pageable", "fused", pageable),
+                  ("fused_pageable_driver_staged", "fused", pageable)]
+    if world > 1:
+        host_cases += [("sharded_pinned", "sharded", h_slice), ("sharded_pageable", "sharded", pageable[col0 * 32:(col0 + ncols) * 32])]
+    for name, fused, src in host_cases:
+        if only and not name.startswith(only if only != "overlap" else "separate"):
             continue
         be.set_staging(name.endswith("driver_staged"))  # A/B: the driver's own pageable path instead of the library's ring
         for _ in range(2):
@@ -261,16 +280,19 @@ def own_arm(args):
     if world == 1:
         h2d = (n if e2e_key.startswith("fused") else 2 * n) * 32 + 32
         d2h = 48 + 32 + 48
+    elif e2e_key.startswith("sharded"):
+        h2d = ncols * 32 + 64 + 128 + world * 128 + 224
+        d2h = 128 + world * 128 + 224 + 128
     else:
-        h2d = (n if e2e_key.startswith("fused") else n + ncols) * 32 + 32
-        d2h = 96 + 32 + 96 + world * 224
+        h2d = (n if e2e_key.startswith("fused") else n + ncols) * 32 + 32 + 224
+        d2h = 96 + 32 + 96 + 128
 
     # ---- per-kernel timing (CUDA events inside the library, on the launching stream) + work counters
     be.profile(True)
     be.profile_read()
     be.msm_stats()
     prof_steps = max(1, min(args.steps, 5))
-    prof_fn, prof_sep = (step_fused, False) if fused_best else (step_separate, True)
+    prof_fn, prof_sep = (step_sharded, False) if best == "sharded" else (step_fused, False) if fused_best else (step_separate, True)
     for _ in range(prof_steps):
         prof_fn()
         finish(prof_sep)
@@ -307,8 +329,11 @@ def own_arm(args):
             "config": {"workload": WORKLOAD,
                        "step": {"separate": "fb_dev_worker_commit + fb_dev_worker_open, one stream",
                                 "overlap": "fb_dev_worker_commit + fb_dev_worker_open on two lanes (fb_ctx_set_lanes(2)), joined",
-                                "fused": "fb_dev_worker_commit_open (both MSMs as one batch over the same resident row)"}[best],
-                       "parallelism": "1 GPU" if world == 1 else "MSM point ranges over %d GPUs + all-gather of %d-byte partials" % (world, 2 * P + 32),
+                                "fused": "fb_dev_worker_commit_open (both MSMs as one batch over the same resident row)",
+                                "sharded": "fb_dev_commit_open_shard_begin + all-gather of 128-byte states + _finish (field half and "
+                                           "MSMs over this rank's slice only)"}[best]
+                               + ("" if world == 1 else "; then all-gather of 224-byte partials + fb_dev_combine_commit_open on every rank"),
+                       "parallelism": "1 GPU" if world == 1 else "MSM point ranges over %d GPUs + all-gather of %d-byte partials + device-side sum" % (world, 2 * P + 32),
                        "l2": "inputs larger than L2: window tables %.2f GB per GPU + 32 MiB coefficients" %
                              (table_windows * ncols * 128 / 1e9), "window_bits": wbits, "msm_split": msm_split,
                        "srs_setup_s": round(setup_s, 2),

@@ -75,6 +75,11 @@ SYMBOLS = [
     ("fb_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
     ("fb_dev_worker_commit_open", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     ("fb_dev_worker_commit_open_partial", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    ("fb_worker_commit_open_shard_begin", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, C.c_uint64, _u8p, _u8p]),
+    ("fb_worker_commit_open_shard_finish", C.c_int, [_ctx, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
+    ("fb_dev_commit_open_shard_begin", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    ("fb_dev_commit_open_shard_finish", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    ("fb_dev_combine_commit_open", C.c_int, [_ctx, C.c_void_p, C.c_uint64, C.c_void_p]),
     ("fb_dev_evaluate_noalloc", C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fb_launch_count", C.c_uint64, [_ctx]),
     ("fb_prof_enable", C.c_int, [_ctx, C.c_int]),

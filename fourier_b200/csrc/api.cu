@@ -285,6 +285,8 @@ void fb_ctx_destroy(fb_ctx* c) {
     if (c->u_bases.pts && c->u_bases.pts != c->d_u) cudaFree(c->u_bases.pts);
     if (c->y_bases.pts && c->y_bases.pts != c->d_g_tau_y) cudaFree(c->y_bases.pts);
     if (c->d_u) cudaFree(c->d_u);
+    c->shard_buf.release();
+    c->shard_coeffs.release();
     for (int k = 0; k < kMaxLanes; k++) lane_destroy(c->lanes[k]);
     lane_destroy(c->ulane);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);

@@ -129,6 +129,13 @@ void horner_quotient(const Fr* d_a, size_t n, const Fr* d_x, Fr* d_y, Fr* d_q, D
 void evalform_open(const NttTables& tab, const Fr* d_evals, size_t n, size_t batch, const Fr* d_alpha, Fr* d_y, Fr* d_qhat,
                    DevBuf& scratch, cudaStream_t st);
 
+// the same for one column shard (elements j0 .. j0+cnt-1 of the row): begin -> 4 Fr of state per shard, exchanged between
+// the shards; finish -> y and the shard's slice of q_hat.  `session` must be the same buffer in both calls.
+void evalform_shard_begin(const NttTables& tab, const Fr* d_evals_slice, size_t n, size_t j0, size_t cnt, const Fr* d_alpha,
+                          Fr* d_state, DevBuf& session, cudaStream_t st);
+void evalform_shard_finish(const NttTables& tab, const Fr* d_evals_slice, size_t n, size_t j0, size_t cnt, const Fr* d_alpha,
+                           const Fr* d_states, int nparts, Fr* d_y, Fr* d_qhat_slice, DevBuf& session, cudaStream_t st);
+
 // ---------------------------------------------------------------- MSM (msm.cu)
 // Window-table entries are padded to one 128-byte line (x in the first 64-byte DRAM atom):
 // a gathered point is exactly one line, and the batched-affine rounds' first pass, which
@@ -186,6 +193,8 @@ void g1_serialize_batch(const G1Affine* d_in, uint8_t* d_out96, size_t n, cudaSt
 void g1_xyzz_to_affine_batch(const G1Xyzz* d_in, G1Affine* d_out, size_t n, cudaStream_t st);
 // out[k] = scalars[k] * G (fixed-base comb on the generator), scalars Montgomery Fr
 void g1_fixed_base_mul(const Fr* d_scalars, size_t n, G1Affine* d_out, DevBuf& scratch, cudaStream_t st);
+// sum of the shards' partial commitments / proofs (nparts x (96 | 32 | 96) bytes) -> 48 | 32 | 48 bytes, on the device
+void g1_combine_parts(const uint8_t* d_parts224, size_t nparts, uint8_t* d_out128, int* d_err, cudaStream_t st);
 // d_out (1 XYZZ) = sum of n affine points (tree sum)
 void g1_sum_affine(const G1Affine* d_in, size_t n, G1Xyzz* d_out, DevBuf& scratch, cudaStream_t st);
 

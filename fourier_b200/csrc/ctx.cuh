@@ -97,6 +97,12 @@ struct fb_ctx {
     std::vector<uint8_t> g2_bytes[3];  // g2, g2^tauX, g2^tauY as read / generated (host only)
     int g2_compressed = -1;
 
+    // sharded commit + open (fb_*_commit_open_shard_begin / _finish): what lives between the two halves.  One sharded
+    // open in flight per context.
+    fb::DevBuf shard_buf;     // 1/(w^j - alpha) over the slice, partial sums, constants
+    fb::DevBuf shard_coeffs;  // host form only: the slice's coefficients (Montgomery)
+    uint64_t shard_len = 0, shard_cnt = 0;
+
     cudaStream_t caller_stream() const { return user_stream ? user_stream : own_stream; }
 };
 

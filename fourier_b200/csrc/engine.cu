@@ -690,4 +690,131 @@ int fb_worker_commit_open_partial(fb_ctx* c, uint64_t i, const uint8_t* coeffs_b
     });
 }
 
+// ---- commit + open of one row sharded by columns, field half included.
+// With fb_worker_commit_open_partial every shard still runs the field half over the WHOLE row (and uploads it).  Here a
+// shard works on its slice only, in two halves around one exchange of 128 bytes per shard:
+//   begin   inv_j = 1/(w^j - alpha), h_j = w^j inv_j, partial S1 = sum c_j h_j and S0 = sum h_j over the slice -> state
+//   (the caller gathers the states of all shards, e.g. one all-gather of 128 bytes)
+//   finish  S1, S0, y from all states; q_hat_j over the slice; commit and proof partials = one batch-of-two MSM
+// The slice is columns [col0, col0 + ncols) cut to the row length `len`: d_slice holds exactly those coefficients.
+static void shard_span(fb_ctx* c, uint64_t len, uint64_t& lo, uint64_t& cnt) {
+    lo = c->col0 < len ? c->col0 : len;
+    const uint64_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
+    cnt = hi - lo;
+}
+
+static int dev_shard_begin(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_slice, uint64_t len, const Fr* d_alpha, Fr* d_state) {
+    int rc = need_row(c, i, 1);
+    if (rc) return rc;
+    int lg = ilog2_exact(len);
+    if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+    uint64_t lo, cnt;
+    shard_span(c, len, lo, cnt);
+    const NttTables& tab = ctx_ntt_tables(c, L, lg);
+    evalform_shard_begin(tab, d_slice, len, lo, cnt, d_alpha, d_state, c->shard_buf, L->stream);
+    return FB_OK;
+}
+
+// d_out: 96 bytes partial commitment | 32 bytes y | 96 bytes partial proof
+static int dev_shard_finish(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_slice, uint64_t len, const Fr* d_alpha,
+                            const Fr* d_states, uint64_t nparts, uint8_t* d_out) {
+    int rc = need_row(c, i, 1);
+    if (rc) return rc;
+    int lg = ilog2_exact(len);
+    if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+    if (nparts == 0 || nparts > 4096) return ctx_fail(c, FB_ERR_ARG, "number of shard states out of range");
+    uint64_t lo, cnt;
+    shard_span(c, len, lo, cnt);
+    const NttTables& tab = ctx_ntt_tables(c, L, lg);
+    Fr* d_y = (Fr*)L->eng_a.get(4 * sizeof(Fr));
+    Fr* d_qhat = L->fr_b.as<Fr>(cnt + 1);
+    evalform_shard_finish(tab, d_slice, len, lo, cnt, d_alpha, d_states, (int)nparts, d_y, d_qhat, c->shard_buf, L->stream);
+    G1Xyzz* d_r = L->small.as<G1Xyzz>(3);
+    lane_msm(c, L, row_bases(c, i), d_slice, cnt, 2, d_r, d_qhat);
+    fr_to_be(d_y, d_out + 96, 1, L->stream);
+    G1Affine* aff = L->pt_b.as<G1Affine>(3);
+    prof_mark("out.affine_compress", L->stream);
+    g1_xyzz_to_affine_batch(d_r, aff, 2, L->stream);
+    g1_serialize_batch(aff, d_out, 1, L->stream);
+    g1_serialize_batch(aff + 1, d_out + 128, 1, L->stream);
+    return FB_OK;
+}
+
+int fb_dev_commit_open_shard_begin(fb_ctx* c, uint64_t i, const void* d_coeffs_slice, uint64_t len, const void* d_alpha,
+                                   void* d_out_state128) {
+    return ctx_call(c, FB_CALL_UTIL, [&](fb_lane* L) -> int {
+        return dev_shard_begin(c, L, i, (const Fr*)d_coeffs_slice, len, (const Fr*)d_alpha, (Fr*)d_out_state128);
+    });
+}
+int fb_dev_commit_open_shard_finish(fb_ctx* c, uint64_t i, const void* d_coeffs_slice, uint64_t len, const void* d_alpha,
+                                    const void* d_states, uint64_t nparts, void* d_out224) {
+    return ctx_call(c, FB_CALL_UTIL, [&](fb_lane* L) -> int {
+        return dev_shard_finish(c, L, i, (const Fr*)d_coeffs_slice, len, (const Fr*)d_alpha, (const Fr*)d_states, nparts,
+                                (uint8_t*)d_out224);
+    });
+}
+
+// host forms: the slice's coefficients (wire bytes) go up once in `begin` and stay in the context until `finish`
+int fb_worker_commit_open_shard_begin(fb_ctx* c, uint64_t i, const uint8_t* coeffs_slice_be, uint64_t slice_len, uint64_t len,
+                                      const uint8_t alpha_be[32], uint8_t out_state128[128]) {
+    return ctx_call(c, FB_CALL_HOST, [&](fb_lane* L) -> int {
+        uint64_t lo, cnt;
+        shard_span(c, len, lo, cnt);
+        if (slice_len != cnt) return ctx_fail(c, FB_ERR_ARG, "the slice must hold exactly the resident columns of the row");
+        ctx_reset_err(c, L);
+        Fr* d_alpha = ctx_upload_fr(c, L, L->small, L->pt_a, alpha_be, 1);
+        Fr* d_s = c->shard_coeffs.as<Fr>(cnt + 1);
+        if (cnt) {
+            uint8_t* d_b = L->in_bytes.as<uint8_t>(cnt * 32 + 64);
+            prof_mark("h2d", L->stream);
+            lane_h2d(c, L, d_b, coeffs_slice_be, cnt * 32);
+            fr_from_be(d_b, d_s, cnt, L->d_err, L->stream);
+        }
+        Fr* d_state = (Fr*)L->eng_a.get(8 * sizeof(Fr));
+        int rc = dev_shard_begin(c, L, i, d_s, len, d_alpha, d_state + 4);
+        if (rc) return rc;
+        c->shard_len = len;
+        c->shard_cnt = cnt;
+        FB_CUDA(cudaMemcpyAsync(L->h_pinned, d_state + 4, 128, cudaMemcpyDeviceToHost, L->stream));
+        rc = ctx_check_err(c, L);
+        if (rc) return rc;
+        memcpy(out_state128, L->h_pinned, 128);
+        return FB_OK;
+    });
+}
+
+int fb_worker_commit_open_shard_finish(fb_ctx* c, uint64_t i, const uint8_t* states128, uint64_t nparts, const uint8_t alpha_be[32],
+                                       uint8_t out_commit96[96], uint8_t out_y_be[32], uint8_t out_proof96[96]) {
+    return ctx_call(c, FB_CALL_HOST, [&](fb_lane* L) -> int {
+        if (!c->shard_len) return ctx_fail(c, FB_ERR_STATE, "no sharded open in flight: call fb_worker_commit_open_shard_begin first");
+        if (nparts == 0 || nparts > 4096) return ctx_fail(c, FB_ERR_ARG, "number of shard states out of range");
+        ctx_reset_err(c, L);
+        Fr* d_alpha = ctx_upload_fr(c, L, L->small, L->pt_a, alpha_be, 1);
+        uint8_t* d_st = L->in_bytes.as<uint8_t>(nparts * 128 + 64);
+        FB_CUDA(cudaMemcpyAsync(d_st, states128, nparts * 128, cudaMemcpyHostToDevice, L->stream));
+        uint8_t* d_ob = L->out_bytes.as<uint8_t>(256);
+        int rc = dev_shard_finish(c, L, i, (const Fr*)c->shard_coeffs.p, c->shard_len, d_alpha, (const Fr*)d_st, nparts, d_ob);
+        c->shard_len = 0;
+        if (rc) return rc;
+        FB_CUDA(cudaMemcpyAsync(L->h_pinned, d_ob, 224, cudaMemcpyDeviceToHost, L->stream));
+        rc = ctx_check_err(c, L);
+        if (rc) return rc;
+        memcpy(out_commit96, L->h_pinned, 96);
+        memcpy(out_y_be, L->h_pinned + 96, 32);
+        memcpy(out_proof96, L->h_pinned + 128, 96);
+        return FB_OK;
+    });
+}
+
+// the last step of every column-sharded commit + open: add the shards' partials.  d_parts = nparts x (96-byte partial
+// commitment | 32-byte y | 96-byte partial proof) as gathered from the shards; d_out = 48 | 32 | 48 (final, compressed)
+int fb_dev_combine_commit_open(fb_ctx* c, const void* d_parts224, uint64_t nparts, void* d_out128) {
+    return ctx_call(c, FB_CALL_UTIL, [&](fb_lane* L) -> int {
+        if (nparts == 0 || nparts > 4096) return ctx_fail(c, FB_ERR_ARG, "number of parts out of range");
+        prof_mark("out.combine_parts", L->stream);
+        g1_combine_parts((const uint8_t*)d_parts224, (size_t)nparts, (uint8_t*)d_out128, L->d_err + 1, L->stream);
+        return FB_OK;
+    });
+}
+
 }  // extern "C"

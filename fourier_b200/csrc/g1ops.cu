@@ -120,6 +120,36 @@ __global__ void __launch_bounds__(128) k_sum_xyzz(const G1Xyzz* __restrict__ in,
     out[t] = acc;
 }
 
+// parts: nparts x (96 | 32 | 96) bytes; thread 0 adds the commitments' partials, thread 1 the proofs'; y is every
+// part's (they agree) and is copied from part 0.  out: 48 | 32 | 48.
+__global__ void __launch_bounds__(32) k_combine_parts(const uint8_t* __restrict__ parts, size_t nparts, uint8_t* __restrict__ out,
+                                                      int* err) {
+    const int t = threadIdx.x;
+    if (t >= 2) {
+        if (t == 2)
+            for (int k = 0; k < 32; k++) out[48 + k] = parts[96 + k];
+        return;
+    }
+    G1Xyzz acc = G1Xyzz::inf();
+    for (size_t p = 0; p < nparts; p++) {
+        uint8_t buf[96];
+        const uint8_t* src = parts + p * 224 + (t ? 128 : 0);
+        for (int k = 0; k < 96; k++) buf[k] = src[k];
+        G1Affine q;
+        int rc = g1_deserialize(buf, &q);
+        if (rc) {
+            atomicCAS(err, 0, rc);
+            q = G1Affine::inf();
+        }
+        g1_add_mixed(acc, q);
+    }
+    G1Affine r = acc.is_inf() ? G1Affine::inf() : g1_to_affine_with_inv(acc, fe_inv_gcd<FpParams>(acc.zzz));
+    uint8_t o[48];
+    g1_compress(r, o);
+    uint8_t* dst = out + (t ? 80 : 0);
+    for (int k = 0; k < 48; k++) dst[k] = o[k];
+}
+
 // generator comb tables, one per device, built once and published only after the build has finished on the
 // device: contexts on several GPUs (or several contexts on one GPU) may run setup concurrently
 constexpr int kMaxDevices = 64;
@@ -151,6 +181,11 @@ void g1_serialize_batch(const G1Affine* d_in, uint8_t* d_out96, size_t n, cudaSt
 void g1_xyzz_to_affine_batch(const G1Xyzz* d_in, G1Affine* d_out, size_t n, cudaStream_t st) {
     if (!n) return;
     (++fb::g_launches, k_to_affine<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_in, d_out, n));
+    FB_CUDA(cudaGetLastError());
+}
+
+void g1_combine_parts(const uint8_t* d_parts224, size_t nparts, uint8_t* d_out128, int* d_err, cudaStream_t st) {
+    (++fb::g_launches, k_combine_parts<<<1, 32, 0, st>>>(d_parts224, nparts, d_out128, d_err));
     FB_CUDA(cudaGetLastError());
 }
 

@@ -289,6 +289,35 @@ class PianoBackend:
                                                    C.addressof(pi)))
         return y.raw, pi.raw
 
+    def commit_open_shard_begin(self, i: int, coeffs_slice: ScalarVec, length: int, alpha) -> bytes:
+        """First half of a commit + open whose field half is sharded too: the slice of the row this context holds -> 128
+        opaque bytes of state, to be gathered over the shards."""
+        buf, n = pack_scalars(coeffs_slice)
+        a = pack_scalar(alpha)
+        st = C.create_string_buffer(128)
+        self._chk(self._lib.fb_worker_commit_open_shard_begin(self._ctx, i, _lib.addr(buf), n, length, _lib.addr(a), C.addressof(st)))
+        return st.raw
+
+    def commit_open_shard_finish(self, i: int, states: bytes, alpha) -> Tuple[bytes, bytes, bytes]:
+        """Second half: the states of all shards -> (partial commitment 96 B, y, partial proof 96 B)."""
+        a = pack_scalar(alpha)
+        cm, y, pi = C.create_string_buffer(96), C.create_string_buffer(FR_BYTES), C.create_string_buffer(96)
+        self._chk(self._lib.fb_worker_commit_open_shard_finish(self._ctx, i, _lib.addr(states), len(states) // 128, _lib.addr(a),
+                                                               C.addressof(cm), C.addressof(y), C.addressof(pi)))
+        return cm.raw, y.raw, pi.raw
+
+    def dev_commit_open_shard_begin(self, i: int, d_slice, length: int, d_alpha, d_state128):
+        self._chk(self._lib.fb_dev_commit_open_shard_begin(self._ctx, i, _lib.addr(d_slice), length, _lib.addr(d_alpha),
+                                                           _lib.addr(d_state128)))
+
+    def dev_commit_open_shard_finish(self, i: int, d_slice, length: int, d_alpha, d_states, nparts: int, d_out224):
+        self._chk(self._lib.fb_dev_commit_open_shard_finish(self._ctx, i, _lib.addr(d_slice), length, _lib.addr(d_alpha),
+                                                            _lib.addr(d_states), nparts, _lib.addr(d_out224)))
+
+    def dev_combine_commit_open(self, d_parts224, nparts: int, d_out128):
+        """Adds the shards' partials on the device: nparts x (96 | 32 | 96) -> 48 | 32 | 48."""
+        self._chk(self._lib.fb_dev_combine_commit_open(self._ctx, _lib.addr(d_parts224), nparts, _lib.addr(d_out128)))
+
     def dev_worker_commit_partial(self, i: int, d_coeffs, count: int, d_out96):
         self._chk(self._lib.fb_dev_worker_commit_partial(self._ctx, i, _lib.addr(d_coeffs), count, _lib.addr(d_out96)))
 

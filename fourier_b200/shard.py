@@ -39,6 +39,22 @@ def all_gather_bytes(dist, blob: bytes, device=None) -> List[bytes]:
     return [flat[k * len(blob):(k + 1) * len(blob)] for k in range(world)]
 
 
+def sharded_commit_open(be, dist, i: int, coeffs_slice, length: int, alpha, device=None, combine=None):
+    """Commit + open of row i with BOTH halves sharded by columns: every rank passes only its slice of the row.
+
+    begin (partial sums over the slice) -> all-gather of the 128-byte states -> finish (y, partial commitment and partial
+    proof over the slice) -> all-gather of the 224-byte partials -> sum.  `be` is this rank's column-sharded backend;
+    `combine(parts)` adds the gathered partials (default: the backend's host-side sum).  Returns (commitment48, y32, proof48),
+    identical on every rank and to the unsharded worker_commit / worker_open."""
+    state = be.commit_open_shard_begin(i, coeffs_slice, length, alpha)
+    states = b"".join(all_gather_bytes(dist, state, device))
+    c96, y, p96 = be.commit_open_shard_finish(i, states, alpha)
+    parts = all_gather_bytes(dist, c96 + y + p96, device)
+    if combine is not None:
+        return combine(parts)
+    return (be.g1_sum(b"".join(p[:96] for p in parts), fmt=96), y, be.g1_sum(b"".join(p[128:224] for p in parts), fmt=96))
+
+
 def pack_rows(commits: Sequence[bytes], ys: Sequence[bytes], proofs: Sequence[bytes]) -> bytes:
     """Per-rank row results as one blob: all commitments, then all evaluations, then all proofs."""
     assert len(commits) == len(ys) == len(proofs)

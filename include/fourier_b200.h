@@ -145,6 +145,18 @@ int fb_worker_commit_open_partial(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs
                                   const uint8_t alpha_be[32], uint8_t out_commit96[96], uint8_t out_y_be[32],
                                   uint8_t out_proof96[96]);
 
+/* Column shards with the field half sharded too (extension): a shard uploads and works on ITS slice of the row only.
+ * begin: coeffs_slice_be = the slice_len coefficients of columns [col0, col0+ncols) cut to the row length len (a power
+ * of two); writes 128 opaque bytes of state (this shard's partial sums).  The caller gathers the states of all shards in
+ * any order (e.g. one all-gather) and gives them to finish, which returns the partial commitment and partial proof (96
+ * bytes each, to be added over the shards: fb_g1_sum / fb_dev_combine_commit_open) and y.  The slice stays resident in
+ * the context between the two calls: one sharded open in flight per context.  Same bytes as the unsharded calls. */
+int fb_worker_commit_open_shard_begin(fb_ctx* ctx, uint64_t i, const uint8_t* coeffs_slice_be, uint64_t slice_len,
+                                      uint64_t len, const uint8_t alpha_be[32], uint8_t out_state128[128]);
+int fb_worker_commit_open_shard_finish(fb_ctx* ctx, uint64_t i, const uint8_t* states128, uint64_t nparts,
+                                       const uint8_t alpha_be[32], uint8_t out_commit96[96], uint8_t out_y_be[32],
+                                       uint8_t out_proof96[96]);
+
 /* ---- engine: master side ------------------------------------------------------
  * replaces PianoBackend::master_commit (piano.rs:164-175): sum of the commitments */
 int fb_master_commit(fb_ctx* ctx, const uint8_t* commitments48, uint64_t count, uint8_t out48[48]);
@@ -225,6 +237,16 @@ int fb_dev_worker_commit_open(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, 
 /* column shard: d_out = 96 bytes partial commitment | 32 bytes y | 96 bytes partial proof */
 int fb_dev_worker_commit_open_partial(fb_ctx* ctx, uint64_t i, const void* d_coeffs_fr, uint64_t len,
                                       const void* d_alpha_fr, void* d_out224);
+
+/* sharded field half, operands in HBM: d_coeffs_slice_fr = the resident columns' coefficients (Montgomery), d_states =
+ * nparts x 128 bytes as gathered; d_out224 = 96 | 32 | 96.  Both run on the caller's stream (fb_ctx_set_stream). */
+int fb_dev_commit_open_shard_begin(fb_ctx* ctx, uint64_t i, const void* d_coeffs_slice_fr, uint64_t len,
+                                   const void* d_alpha_fr, void* d_out_state128);
+int fb_dev_commit_open_shard_finish(fb_ctx* ctx, uint64_t i, const void* d_coeffs_slice_fr, uint64_t len,
+                                    const void* d_alpha_fr, const void* d_states, uint64_t nparts, void* d_out224);
+/* adds the shards' partials on the device: d_parts224 = nparts x (96-byte partial commitment | 32-byte y | 96-byte partial
+ * proof) -> d_out128 = 48-byte commitment | 32-byte y | 48-byte proof.  On the caller's stream. */
+int fb_dev_combine_commit_open(fb_ctx* ctx, const void* d_parts224, uint64_t nparts, void* d_out128);
 
 /* uncompressed (96-byte) result, for the partial sums of an MSM sharded by point ranges */
 int fb_dev_msm_partial(fb_ctx* ctx, const fb_bases* b, const void* d_scalars_fr, uint64_t count, void* d_out96);

@@ -72,6 +72,74 @@ def test_column_shards_sum_to_the_unsharded_result(gpu, n, shards):
     full.close()
 
 
+@pytest.mark.parametrize("n,length,shards", [(12, 1 << 12, 2), (12, 1 << 12, 3), (14, 1 << 14, 4), (12, 1 << 10, 4), (12, 2, 4), (18, 1 << 18, 8)])
+def test_sharded_field_half_matches_the_unsharded_calls(gpu, n, length, shards):
+    """fb_worker_commit_open_shard_begin / _finish: every shard uploads and works on its slice only; the 128-byte states are
+    exchanged; the partials summed (host g1_sum and the device combine) equal worker_commit / worker_open of the whole row
+    and the known-tau oracle.  alpha outside the domain, on the domain (the index lands in exactly one shard's slice), and
+    rows shorter than the resident width (some shards hold no element of the row)."""
+    import torch
+    from fourier_b200 import PianoBackend, shard
+    T = 1 << n
+    rng = random.Random(n * 131 + shards + length)
+    coeffs = [rng.randrange(R) for _ in range(length)]
+    cb = fr_list_to_bytes(coeffs)
+    full = PianoBackend(n, 0)
+    full.setup(SECRET_X, SECRET_Y)
+    bes = []
+    for k in range(shards):
+        col0, ncols = shard.split_range(T, shards, k)
+        b = PianoBackend(n, 0)
+        b.set_col_shard(col0, ncols)
+        b.setup(SECRET_X, SECRET_Y)
+        bes.append((b, col0, ncols))
+    w = bls.root_of_unity(length.bit_length() - 1)
+    alphas = [rng.randrange(R), pow(w, (length * 5) // 7, R), 1]
+    if n <= 14:
+        o = known_tau_oracle(n, 0)
+    dev = torch.device("cuda", 0)
+    for alpha in alphas:
+        want_c = full.worker_commit(0, cb)
+        want_y, want_p = full.worker_open(0, cb, alpha)
+        if n <= 14 and length == T:
+            assert want_c == bls.g1_compress(o.worker_commit_known_tau(0, coeffs))
+            oy, opi = o.worker_open_known_tau(0, coeffs, alpha)
+            assert (want_y, want_p) == (oy.to_bytes(32, "big"), bls.g1_compress(opi))
+        states = []
+        for b, col0, ncols in bes:
+            lo, hi = min(col0, length), min(col0 + ncols, length)
+            states.append(b.commit_open_shard_begin(0, cb[32 * lo:32 * hi], length, alpha))
+        gathered = b"".join(reversed(states))  # any order
+        parts = []
+        for b, col0, ncols in bes:
+            c96, y, p96 = b.commit_open_shard_finish(0, gathered, alpha)
+            assert y == want_y
+            parts.append((c96, y, p96))
+        assert full.g1_sum(b"".join(c for c, _, _ in parts), fmt=96) == want_c
+        assert full.g1_sum(b"".join(p for _, _, p in parts), fmt=96) == want_p
+        # the device combine of the gathered 224-byte records
+        d_parts = torch.frombuffer(bytearray(b"".join(c + y + p for c, y, p in parts)), dtype=torch.uint8).to(dev)
+        d_out = torch.zeros(128, dtype=torch.uint8, device=dev)
+        full.dev_combine_commit_open(d_parts, shards, d_out)
+        full.sync()
+        assert bytes(d_out.cpu().numpy()) == want_c + want_y + want_p
+    from fourier_b200 import FourierError
+    with pytest.raises(FourierError):  # finish without begin
+        bes[0][0].commit_open_shard_finish(0, bytes(128 * shards), 5)
+    with pytest.raises(FourierError):  # a slice of the wrong length
+        bes[0][0].commit_open_shard_begin(0, cb[:32], length * 2 if length * 2 <= T else length // 2, 5)
+    if length >= shards:
+        bad = bytearray(cb)
+        bad[0:32] = R.to_bytes(32, "big")  # shard 0 owns coefficient 0
+        with pytest.raises(FourierError) as ei:
+            lo, hi = 0, min(bes[0][2], length)
+            bes[0][0].commit_open_shard_begin(0, bytes(bad[32 * lo:32 * hi]), length, 5)
+        assert "Invalid scalar" in str(ei.value)
+    for b, _, _ in bes:
+        b.close()
+    full.close()
+
+
 def test_column_shard_rejects_bad_scalar_in_its_slice(gpu):
     """fb_worker_commit_partial uploads only its slice, so the shard that owns an out-of-range scalar
     is the one that says "Invalid scalar" (some shard always does); the open uploads the full row."""

@@ -12,6 +12,74 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+class OracleShardBackend:
+    """The sharded commit + open protocol (begin -> states -> finish -> partials) restated on the ORACLE's big-int
+    arithmetic with a known-tau SRS (m = 0): test infrastructure for the host logic of shard.sharded_commit_open."""
+
+    def __init__(self, o, bls, col0, ncols):
+        self.o, self.bls, self.col0, self.ncols = o, bls, col0, ncols
+        self.slice = None
+
+    def _span(self, length):
+        lo, hi = min(self.col0, length), min(self.col0 + self.ncols, length)
+        return lo, hi
+
+    def commit_open_shard_begin(self, i, coeffs_slice, length, alpha):
+        R = self.bls.R
+        lo, hi = self._span(length)
+        assert len(coeffs_slice) == hi - lo
+        w = self.bls.root_of_unity(length.bit_length() - 1)
+        s1 = s0 = ck = 0
+        k = -1
+        self.inv = []
+        for jj, c in enumerate(coeffs_slice):
+            wj = pow(w, lo + jj, R)
+            d = (wj - alpha) % R
+            if d == 0:
+                k, ck = lo + jj, c
+                self.inv.append(0)
+                continue
+            inv = pow(d, -1, R)
+            self.inv.append(inv)
+            s1 = (s1 + c * wj * inv) % R
+            s0 = (s0 + wj * inv) % R
+        self.slice, self.length = list(coeffs_slice), length
+        return b"".join(v.to_bytes(32, "big") for v in (s1, s0, ck)) + (k % (1 << 64)).to_bytes(8, "big") + bytes(24)
+
+    def commit_open_shard_finish(self, i, states, alpha):
+        bls, R, length = self.bls, self.bls.R, self.length
+        lo, hi = self._span(length)
+        s1 = s0 = ck = 0
+        k = -1
+        for p in range(len(states) // 128):
+            st = states[128 * p:128 * p + 128]
+            s1 = (s1 + int.from_bytes(st[:32], "big")) % R
+            s0 = (s0 + int.from_bytes(st[32:64], "big")) % R
+            kk = int.from_bytes(st[96:104], "big")
+            if kk != (1 << 64) - 1 and k < 0:
+                k, ck = kk, int.from_bytes(st[64:96], "big")
+        w = bls.root_of_unity(length.bit_length() - 1)
+        if k < 0:
+            y = (-(pow(alpha, length, R) - 1) * pow(length, -1, R) * s1) % R
+        else:
+            y = ck
+        qhat = []
+        for jj, c in enumerate(self.slice):
+            if lo + jj == k:
+                qhat.append((-pow(w, -k, R) * (s1 - c * s0)) % R)
+            else:
+                qhat.append((c - y) * self.inv[jj] % R)
+        lag = self.o.settings.l_at_tau  # length == T here
+        part = lambda v: bls.g1_serialize(bls.g1_mul(bls.G1_GEN, sum(a * lag[lo + jj] for jj, a in enumerate(v)) % R))
+        return part(self.slice), y.to_bytes(32, "big"), part(qhat)
+
+    def g1_sum(self, blob, fmt=96):
+        total = self.bls.G1_INF
+        for k in range(len(blob) // fmt):
+            total = self.bls.g1_add(total, self.bls.g1_deserialize(blob[fmt * k:fmt * (k + 1)]))
+        return self.bls.g1_compress(total)
+
+
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -48,7 +116,21 @@ def _worker(rank, world, port, q):
         gc, gy, gp = shard.unpack_rows(shard.all_gather_bytes(dist, blob), counts)
         ok_rows = (gc == [bytes([i]) * 48 for i in range(M)] and gy == [bytes([100 + i]) * 32 for i in range(M)]
                    and gp == [bytes([200 + i]) * 48 for i in range(M)])
-        q.put((rank, ok_msm, ok_rows))
+        # (3) commit + open with the field half sharded too: begin -> all-gather states -> finish -> all-gather partials
+        from oracle import piano as opiano
+        n = 4
+        o = opiano.PianoOracle(n, 0)
+        o.generate_trusted_setup(bytes([1] * 32), bytes([2] * 32), with_points=False)
+        row = [rng.randrange(R) for _ in range(o.T)]
+        ok_shard = True
+        for alpha in (rng.randrange(R), pow(bls.root_of_unity(n), 11, R)):  # outside the domain; on it (index 11 -> rank 1's slice)
+            col0, ncols = shard.split_range(o.T, world, rank)
+            be = OracleShardBackend(o, bls, col0, ncols)
+            got = shard.sharded_commit_open(be, dist, 0, row[col0:col0 + ncols], o.T, alpha)
+            oy, opi = o.worker_open_known_tau(0, row, alpha)
+            want = (bls.g1_compress(o.worker_commit_known_tau(0, row)), oy.to_bytes(32, "big"), bls.g1_compress(opi))
+            ok_shard = ok_shard and got == want
+        q.put((rank, ok_msm, ok_rows and ok_shard))
     finally:
         dist.destroy_process_group()
 
