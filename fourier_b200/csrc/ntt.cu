@@ -88,7 +88,7 @@ struct PassArgs {
     const Fr* tile_tw;
     const Fr* n_inv;
     unsigned long long batch_stride;  // elements between consecutive transforms of a batch (blockIdx.y)
-    int pipe;  // 1: cp.async tile loads + twiddle prefetch in batches of kOutBatch (default); 0: the plain loops (A/B)
+    int pipe;  // 1: the tile is loaded with cp.async (small transforms: latency-bound, see ntt_run)
 };
 
 // 16-byte asynchronous copy global -> shared (LDGSTS): the whole tile is in flight at once, with no register staging
@@ -97,7 +97,6 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-constexpr int kOutBatch = 4;  // inter-pass twiddles fetched ahead per thread in the output phase
 
 __device__ __forceinline__ Fr lds_fr(const uint4* p0, const uint4* p1, uint32_t e) {
     Fr r;
@@ -251,16 +250,14 @@ __global__ void __launch_bounds__(256, MINB) k_ntt_pass(PassArgs a) {
             k = e >> a.log_b;
         }
     };
-    auto emit = [&](uint32_t k, uint32_t cb, const Fr* tw) {
+    auto emit = [&](uint32_t k, uint32_t cb) {
         uint32_t pos = __brev(k) >> (32 - a.log_r);
         if (a.log_r == 0) pos = 0;
         Fr val = lds_fr(s0, s1, (pos << a.log_b) | cb);
         const unsigned long long c = c0 + cb;
         const unsigned long long rest = c >> a.log_q;
         if (a.twiddle) {
-            if (tw) {
-                val = fe_mul<FrParams>(val, *tw);
-            } else if (a.tw_full) {
+            if (a.tw_full) {
                 val = fe_mul<FrParams>(val, ldg_fr(a.tw_full + (unsigned long long)k * rest));
             } else {
                 unsigned long long x = ((unsigned long long)k * rest) << a.log_q;
@@ -274,35 +271,10 @@ __global__ void __launch_bounds__(256, MINB) k_ntt_pass(PassArgs a) {
         dst[0] = make_uint4(val.v[0], val.v[1], val.v[2], val.v[3]);
         dst[1] = make_uint4(val.v[4], val.v[5], val.v[6], val.v[7]);
     };
-    if (a.pipe && a.twiddle && a.tw_full) {
-        // the single-multiply twiddles of kOutBatch elements are requested before the first of them is used
-        for (uint32_t e0 = tid; e0 < tile; e0 += kOutBatch * nt) {
-            Fr tw[kOutBatch];
-#pragma unroll
-            for (int i = 0; i < kOutBatch; i++) {
-                const uint32_t e = e0 + (uint32_t)i * nt;
-                if (e < tile) {
-                    uint32_t k, cb;
-                    coords(e, k, cb);
-                    tw[i] = ldg_fr(a.tw_full + (unsigned long long)k * ((c0 + cb) >> a.log_q));
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < kOutBatch; i++) {
-                const uint32_t e = e0 + (uint32_t)i * nt;
-                if (e < tile) {
-                    uint32_t k, cb;
-                    coords(e, k, cb);
-                    emit(k, cb, &tw[i]);
-                }
-            }
-        }
-    } else {
-        for (uint32_t e = tid; e < tile; e += nt) {
-            uint32_t k, cb;
-            coords(e, k, cb);
-            emit(k, cb, nullptr);
-        }
+    for (uint32_t e = tid; e < tile; e += nt) {
+        uint32_t k, cb;
+        coords(e, k, cb);
+        emit(k, cb);
     }
 }
 
@@ -322,7 +294,7 @@ static int ntt_tile_log() { static int v = env_int("FB_NTT_TILE", kTileLog); ret
 static int ntt_group_stages() { static int v = env_int("FB_NTT_G", 2); return v == 3 ? 3 : 2; }
 static int ntt_threads_div() { static int v = env_int("FB_NTT_TDIV", 4); return v < 2 ? 2 : (v > 16 ? 16 : v); }
 static int ntt_full_table_log() { static int v = env_int("FB_NTT_FULL", kNttFullTableLog); return v; }
-static int ntt_pipe() { static int v = env_int("FB_NTT_PIPE", 1); return v ? 1 : 0; }
+static int ntt_pipe() { static int v = env_int("FB_NTT_PIPE", -1); return v; }  // -1: by size
 static int ntt_max_log_b() { static int v = env_int("FB_NTT_MAXB", 3); return v < 0 ? 0 : v; }
 
 NttPlan ntt_make_plan(int log_n) {
@@ -456,7 +428,12 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
         prof_mark(names[j], st);
         a.batch_stride = 1ull << log_n;
-        a.pipe = ntt_pipe();
+        // Measured on B200 (profiles/r2_v4_ntt_pipe_ab.txt): with cp.async a thread's tile loads no longer wait for one
+        // another (LDG -> STS pairs serialise on the scoreboard), which helps where nothing else hides the latency -
+        // 2^16: 0.0325 -> 0.0312 ms - and costs 3-10 % at 2^18 / 2^20 where three resident CTAs per SM already overlap
+        // one another's phases; fetching the inter-pass twiddles four elements ahead in the output phase cost 6 % at 2^22+
+        // (registers) and is not kept.
+        a.pipe = ntt_pipe() >= 0 ? (ntt_pipe() & 1) : ((batch << log_n) <= ((size_t)1 << 16) ? 1 : 0);
         const dim3 grid((unsigned)blocks, (unsigned)batch);
         if (ntt_group_stages() == 3) (++fb::g_launches, k_ntt_pass<3, 2><<<grid, threads, smem, st>>>(a));
         else (++fb::g_launches, k_ntt_pass<2, 3><<<grid, threads, smem, st>>>(a));
