@@ -15,4 +15,4 @@ except Exception as e: print("  failed", e)
 PY
 }
 run kzg --steps 10 --warmup 3
-for w in ${WORKLOADS:-msm bipoly ntt}; do run $w --workload $w --steps 3 --warmup 3; done
+for w in ${WORKLOADS-msm bipoly ntt}; do run $w --workload $w --steps 3 --warmup 3; done
