@@ -428,7 +428,7 @@ void ntt_run(const NttTables& tab, const TileTwiddles& tt, const Fr* in, Fr* out
         static const char* const names[4] = {"ntt.pass0", "ntt.pass1", "ntt.pass2", "ntt.pass3"};
         prof_mark(names[j], st);
         a.batch_stride = 1ull << log_n;
-        // Measured on B200 (profiles/r2_v4_ntt_pipe_ab.txt): with cp.async a thread's tile loads no longer wait for one
+        // Measured on B200 (profiles/r2_v4_rejected_ntt_pipe_msm_ring.txt): with cp.async a thread's tile loads no longer wait for one
         // another (LDG -> STS pairs serialise on the scoreboard), which helps where nothing else hides the latency -
         // 2^16: 0.0325 -> 0.0312 ms - and costs 3-10 % at 2^18 / 2^20 where three resident CTAs per SM already overlap
         // one another's phases; fetching the inter-pass twiddles four elements ahead in the output phase cost 6 % at 2^22+
