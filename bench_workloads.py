@@ -276,6 +276,8 @@ def run_msm(args, env=None, emit=True):
     assert hres == res, "host-API and device-resident results differ"
 
     be.profile(True)
+    step_device()  # (scratch of the single-stream shape grows here, untimed)
+    torch.cuda.synchronize()
     be.profile_read()
     be.msm_stats()
     step_device()
@@ -362,12 +364,17 @@ def run_bipoly(args, env=None, emit=True):
     d_c, d_y, d_p = d_out[:rows * 48], d_out[rows * 48:rows * 80], d_out[rows * 80:]
     gathered = torch.zeros(world * rows * 128, dtype=torch.uint8, device=dev) if world > 1 else None
 
-    be.set_lanes(int(os.environ.get("FB_BENCH_LANES", "1")))
+    be.set_lanes(int(os.environ.get("FB_BENCH_LANES", "2")))
     be.set_msm_split(int(os.environ.get("FB_BENCH_SPLIT", "1")))
 
+    fused_rows = os.environ.get("FB_BENCH_ROWS", "fused") == "fused"  # "two": dev_commit_rows + dev_open_rows on two lanes
+
     def step_device():
-        be.dev_commit_rows(row0, rows, d_coeffs, T, d_c)
-        be.dev_open_rows(row0, rows, d_coeffs, T, d_alpha, d_y, d_p)
+        if fused_rows:
+            be.dev_commit_open_rows(row0, rows, d_coeffs, T, d_alpha, d_c, d_y, d_p)
+        else:
+            be.dev_commit_rows(row0, rows, d_coeffs, T, d_c)
+            be.dev_open_rows(row0, rows, d_coeffs, T, d_alpha, d_y, d_p)
         be.join()
         if world > 1:
             dist.all_gather_into_tensor(gathered, d_out)
@@ -395,8 +402,11 @@ def run_bipoly(args, env=None, emit=True):
 
     # e2e: host coefficient rows through commit_rows / open_rows, gather, master step on rank 0
     def step_host():
-        c = be.commit_rows(row0, rows, h_coeffs)
-        y, p = be.open_rows(row0, rows, h_coeffs, alpha_b)
+        if fused_rows:
+            c, y, p = be.commit_open_rows(row0, rows, h_coeffs, alpha_b)
+        else:
+            c = be.commit_rows(row0, rows, h_coeffs)
+            y, p = be.open_rows(row0, rows, h_coeffs, alpha_b)
         blob = shard.pack_rows(c, y, p)
         if world > 1:
             mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
@@ -420,6 +430,8 @@ def run_bipoly(args, env=None, emit=True):
 
     be.set_lanes(1)
     be.profile(True)
+    step_device()  # (scratch of the single-stream shape grows here, untimed)
+    torch.cuda.synchronize()
     be.profile_read()
     be.msm_stats()
     step_device()
@@ -448,8 +460,9 @@ def run_bipoly(args, env=None, emit=True):
                                       "128 bytes per row, master step on rank 0" % (world, rows),
                        "l2": "inputs larger than L2 (window tables of the local rows + coefficient matrix)",
                        "srs_setup_s": round(setup_s, 2), "window_bits": wbits, "windows": nwin,
-                       "lanes": int(os.environ.get("FB_BENCH_LANES", "1")), "msm_split": int(os.environ.get("FB_BENCH_SPLIT", "1"))},
-            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": 2 * rows * T * 32 + 32,
+                       "lanes": int(os.environ.get("FB_BENCH_LANES", "2")),
+                       "step": "fb_dev_commit_open_rows (one call; commit MSMs on a sub-stream)" if fused_rows else "fb_dev_commit_rows + fb_dev_open_rows on two lanes", "msm_split": int(os.environ.get("FB_BENCH_SPLIT", "1"))},
+            "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": (1 if fused_rows else 2) * rows * T * 32 + 32,
                     "d2h_bytes_per_step": rows * 128 + (world * rows * 128 if world > 1 else 0) + 128,
                     "includes": "master_commit + master_open on rank 0"},
             "gpu_launches": int(launches), "clocks": clk,

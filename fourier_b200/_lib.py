@@ -28,6 +28,7 @@ SYMBOLS = [
     ("fb_ctx_set_open_mode", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_set_staging", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_set_msm_split", C.c_int, [_ctx, C.c_int]),
+    ("fb_ctx_set_pair_mode", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_set_lanes", C.c_int, [_ctx, C.c_int]),
     ("fb_ctx_join", C.c_int, [_ctx]),
     ("fb_srs_generate", C.c_int, [_ctx, _u8p, _u8p, C.c_uint64, C.c_uint64]),
@@ -80,6 +81,8 @@ SYMBOLS = [
     ("fb_dev_commit_open_shard_begin", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     ("fb_dev_commit_open_shard_finish", C.c_int, [_ctx, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     ("fb_dev_combine_commit_open", C.c_int, [_ctx, C.c_void_p, C.c_uint64, C.c_void_p]),
+    ("fb_commit_open_rows", C.c_int, [_ctx, C.c_uint64, C.c_uint64, _u8p, C.c_uint64, _u8p, _u8p, _u8p, _u8p]),
+    ("fb_dev_commit_open_rows", C.c_int, [_ctx, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fb_dev_evaluate_noalloc", C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("fb_launch_count", C.c_uint64, [_ctx]),
     ("fb_prof_enable", C.c_int, [_ctx, C.c_int]),

@@ -187,6 +187,27 @@ void lane_msm(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_scalars,
     msm_run_split(bases, d_scalars, len, batch, true, d_out, ex, d_scalars2);
 }
 
+bool lane_pair_fork(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_a, size_t cnt, G1Xyzz* d_r) {
+    const bool profiling = g_prof && g_prof->on;  // per-phase timing needs one stream
+    bool two = c->pair_mode == 2 || (c->pair_mode == 0 && cnt >= ((size_t)1 << 18));
+    if (profiling || c->msm_split > 1 || cnt == 0) two = false;
+    if (!two) return false;
+    FB_CUDA(cudaEventRecord(L->sub_fork, L->stream));
+    FB_CUDA(cudaStreamWaitEvent(L->sub_stream[0], L->sub_fork, 0));
+    msm_run(bases, d_a, cnt, 1, true, d_r, L->msm_sub[0], L->sub_stream[0]);
+    FB_CUDA(cudaEventRecord(L->sub_join[0], L->sub_stream[0]));
+    return true;
+}
+
+void lane_pair_join(fb_ctx* c, fb_lane* L, bool forked, const MsmBases& bases, const Fr* d_a, const Fr* d_b, size_t cnt, G1Xyzz* d_r) {
+    if (!forked) {
+        lane_msm(c, L, bases, d_a, cnt, 2, d_r, d_b);
+        return;
+    }
+    msm_run(bases, d_b, cnt, 1, true, d_r + 1, L->msm, L->stream);
+    FB_CUDA(cudaStreamWaitEvent(L->stream, L->sub_join[0], 0));
+}
+
 const NttTables& ctx_ntt_tables(fb_ctx* c, fb_lane* L, int log_n) {
     std::lock_guard<std::mutex> lk(c->tab_mu);
     bool built = false;
@@ -368,6 +389,13 @@ int fb_ctx_set_msm_split(fb_ctx* c, int parts) {
     if (!c || parts < 1 || parts > kMaxSplit) return FB_ERR_ARG;
     std::lock_guard<std::mutex> lk(c->mu);
     c->msm_split = parts;
+    return FB_OK;
+}
+
+int fb_ctx_set_pair_mode(fb_ctx* c, int mode) {
+    if (!c || mode < 0 || mode > 2) return FB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->pair_mode = mode;
     return FB_OK;
 }
 

@@ -76,6 +76,7 @@ struct fb_ctx {
     int window_pref = 0;
     int open_mode = 0;    // 0: evaluation form (default); 1: the reference's literal iNTT -> eval -> divide -> NTT
     int msm_split = 1;    // sub-MSMs per MSM (fb_ctx_set_msm_split)
+    int pair_mode = 0;    // commit + open of one row: 0 by size, 1 one batch-of-two pass, 2 two MSMs on two streams (fb_ctx_set_pair_mode)
     int staging = 0;      // 0: pinned ring for pageable host input; 1: hand pageable pointers to cudaMemcpyAsync
 
     std::mutex tab_mu;  // twiddle tables are built on first use, by whichever lane needs them
@@ -119,6 +120,14 @@ void lane_h2d(fb_ctx* c, fb_lane* L, void* d_dst, const void* h_src, size_t byte
 // msm_run on the lane, split into the context's number of sub-MSMs when the job is large enough
 void lane_msm(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batch, G1Xyzz* d_out,
               const Fr* d_scalars2 = nullptr);
+
+// The two MSMs of a commit + open over one base row: d_r[0] = sum a_k P_k, d_r[1] = sum b_k P_k.  Rows of >= 2^18 points run
+// as two plain MSMs on two streams of the lane - lane_pair_fork starts the commit MSM on a sub-stream BEFORE the caller
+// enqueues the field half that produces b, so that it runs under the field half and its latency-bound phases under the
+// other MSM's multiplier-bound ones - smaller rows as one batch-of-two pass (one sort, one reduction).  lane_pair_join runs
+// the second MSM (or the batch of two) on the lane's stream and joins.
+bool lane_pair_fork(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_a, size_t cnt, G1Xyzz* d_r);
+void lane_pair_join(fb_ctx* c, fb_lane* L, bool forked, const MsmBases& bases, const Fr* d_a, const Fr* d_b, size_t cnt, G1Xyzz* d_r);
 
 // run f(lane), mapping exceptions to status codes
 template <class F>

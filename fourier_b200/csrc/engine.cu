@@ -625,11 +625,13 @@ static int dev_commit_open(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_coeffs
     if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
     const NttTables& tab = ctx_ntt_tables(c, L, lg);
     Fr* d_y = (Fr*)L->eng_a.get(4 * sizeof(Fr));
-    Fr* d_qhat = open_scalars(c, L, tab, d_coeffs, len, d_alpha, d_y);
     G1Xyzz* d_r = L->small.as<G1Xyzz>(3);
     const size_t lo = c->col0 < len ? c->col0 : len;
     const size_t hi = c->col0 + c->ncols < len ? c->col0 + c->ncols : len;
-    lane_msm(c, L, row_bases(c, i), d_coeffs + lo, hi - lo, 2, d_r, d_qhat + lo);  // piano.rs:150-158, 228-236
+    const MsmBases bases = row_bases(c, i);
+    const bool forked = lane_pair_fork(c, L, bases, d_coeffs + lo, hi - lo, d_r);  // piano.rs:150-158 (may start now)
+    Fr* d_qhat = open_scalars(c, L, tab, d_coeffs, len, d_alpha, d_y);
+    lane_pair_join(c, L, forked, bases, d_coeffs + lo, d_qhat + lo, hi - lo, d_r);  // :228-236
     fr_to_be(d_y, d_out + fmt, 1, L->stream);
     G1Affine* aff = L->pt_b.as<G1Affine>(3);
     prof_mark("out.affine_compress", L->stream);
@@ -728,9 +730,11 @@ static int dev_shard_finish(fb_ctx* c, fb_lane* L, uint64_t i, const Fr* d_slice
     const NttTables& tab = ctx_ntt_tables(c, L, lg);
     Fr* d_y = (Fr*)L->eng_a.get(4 * sizeof(Fr));
     Fr* d_qhat = L->fr_b.as<Fr>(cnt + 1);
-    evalform_shard_finish(tab, d_slice, len, lo, cnt, d_alpha, d_states, (int)nparts, d_y, d_qhat, c->shard_buf, L->stream);
     G1Xyzz* d_r = L->small.as<G1Xyzz>(3);
-    lane_msm(c, L, row_bases(c, i), d_slice, cnt, 2, d_r, d_qhat);
+    const MsmBases bases = row_bases(c, i);
+    const bool forked = lane_pair_fork(c, L, bases, d_slice, cnt, d_r);
+    evalform_shard_finish(tab, d_slice, len, lo, cnt, d_alpha, d_states, (int)nparts, d_y, d_qhat, c->shard_buf, L->stream);
+    lane_pair_join(c, L, forked, bases, d_slice, d_qhat, cnt, d_r);
     fr_to_be(d_y, d_out + 96, 1, L->stream);
     G1Affine* aff = L->pt_b.as<G1Affine>(3);
     prof_mark("out.affine_compress", L->stream);
@@ -814,6 +818,74 @@ int fb_dev_combine_commit_open(fb_ctx* c, const void* d_parts224, uint64_t npart
         prof_mark("out.combine_parts", L->stream);
         g1_combine_parts((const uint8_t*)d_parts224, (size_t)nparts, (uint8_t*)d_out128, L->d_err + 1, L->stream);
         return FB_OK;
+    });
+}
+
+// ---- commit + open of a block of rows in one call (the bivariate row loop of src/bipoly.rs / benches/piano.rs:41-63 does
+// worker_commit and worker_open of every row): the coefficient matrix goes up once, and the commit MSMs (a batch over the
+// rows) run on a sub-stream of the lane while the field half and the proof MSMs run on the lane's stream.
+static int dev_commit_open_rows(fb_ctx* c, fb_lane* L, uint64_t row0, uint64_t nrows, const Fr* d_all, uint64_t len,
+                                const Fr* d_alpha, uint8_t* d_c48, uint8_t* d_ys_be, uint8_t* d_p48) {
+    int rc = need_row(c, row0, nrows);
+    if (rc) return rc;
+    if ((rc = need_full_cols(c))) return rc;
+    int lg = ilog2_exact(len);
+    if (lg < 0 || len > c->T) return ctx_fail(c, FB_ERR_ARG, "A list with power-of-two length is expected");
+    if (nrows == 0) return FB_OK;
+    const NttTables& tab = ctx_ntt_tables(c, L, lg);
+    Fr* d_ys = (Fr*)L->eng_a.get((nrows + 1) * sizeof(Fr));
+    G1Xyzz* d_rc = (G1Xyzz*)L->eng_b.get((2 * nrows + 2) * sizeof(G1Xyzz));
+    G1Xyzz* d_rp = d_rc + nrows;
+    const bool profiling = g_prof && g_prof->on;
+    const bool forked = !profiling && c->msm_split <= 1 && c->pair_mode != 1;
+    if (forked) {
+        FB_CUDA(cudaEventRecord(L->sub_fork, L->stream));
+        FB_CUDA(cudaStreamWaitEvent(L->sub_stream[0], L->sub_fork, 0));
+        msm_run(row_bases(c, row0), d_all, len, nrows, true, d_rc, L->msm_sub[0], L->sub_stream[0]);  // piano.rs:150-158
+        FB_CUDA(cudaEventRecord(L->sub_join[0], L->sub_stream[0]));
+    } else {
+        lane_msm(c, L, row_bases(c, row0), d_all, len, nrows, d_rc);
+    }
+    const uint64_t slab = 4096;
+    for (uint64_t r = 0; r < nrows; r += slab) {
+        const uint64_t rc2 = nrows - r < slab ? nrows - r : slab;
+        Fr* d_qhat = open_scalars(c, L, tab, d_all + r * len, len, d_alpha, d_ys + r, rc2);
+        lane_msm(c, L, row_bases(c, row0 + r), d_qhat, len, rc2, d_rp + r);  // :228-236
+    }
+    if (forked) FB_CUDA(cudaStreamWaitEvent(L->stream, L->sub_join[0], 0));
+    fr_to_be(d_ys, d_ys_be, nrows, L->stream);
+    ctx_points_out(c, L, d_rc, nrows, d_c48);
+    ctx_points_out(c, L, d_rp, nrows, d_p48);
+    return FB_OK;
+}
+
+int fb_dev_commit_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const void* d_coeffs, uint64_t len, const void* d_alpha,
+                            void* d_out_commit48s, void* d_out_ys, void* d_out_proof48s) {
+    return ctx_call(c, FB_CALL_ASYNC, [&](fb_lane* L) -> int {
+        return dev_commit_open_rows(c, L, row0, nrows, (const Fr*)d_coeffs, len, (const Fr*)d_alpha, (uint8_t*)d_out_commit48s,
+                                    (uint8_t*)d_out_ys, (uint8_t*)d_out_proof48s);
+    });
+}
+
+int fb_commit_open_rows(fb_ctx* c, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len, const uint8_t alpha_be[32],
+                        uint8_t* out_commit48s, uint8_t* out_ys_be, uint8_t* out_proof48s) {
+    return ctx_call(c, FB_CALL_HOST, [&](fb_lane* L) -> int {
+        if (nrows == 0) return FB_OK;
+        if (len > c->T) return ctx_fail(c, FB_ERR_ARG, "Supplied list is longer than the available max width");
+        ctx_reset_err(c, L);
+        uint8_t* d_b = L->in_bytes.as<uint8_t>(nrows * len * 32 + 64);
+        prof_mark("h2d", L->stream);
+        lane_h2d(c, L, d_b, coeffs_be, nrows * len * 32);
+        Fr* d_alpha = ctx_upload_fr(c, L, L->small, L->pt_a, alpha_be, 1);
+        Fr* d_all = L->fr_a.as<Fr>(nrows * len + 1);
+        fr_from_be(d_b, d_all, nrows * len, L->d_err, L->stream);
+        uint8_t* d_ob = L->out_bytes.as<uint8_t>(128 * nrows);
+        int rc = dev_commit_open_rows(c, L, row0, nrows, d_all, len, d_alpha, d_ob, d_ob + 48 * nrows, d_ob + 80 * nrows);
+        if (rc) return rc;
+        FB_CUDA(cudaMemcpyAsync(out_commit48s, d_ob, 48 * nrows, cudaMemcpyDeviceToHost, L->stream));
+        FB_CUDA(cudaMemcpyAsync(out_ys_be, d_ob + 48 * nrows, 32 * nrows, cudaMemcpyDeviceToHost, L->stream));
+        FB_CUDA(cudaMemcpyAsync(out_proof48s, d_ob + 80 * nrows, 48 * nrows, cudaMemcpyDeviceToHost, L->stream));
+        return ctx_check_err(c, L);
     });
 }
 

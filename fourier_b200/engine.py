@@ -152,6 +152,10 @@ class PianoBackend:
         """parts >= 2: every large MSM runs as that many sub-MSMs on as many streams of its lane."""
         self._chk(self._lib.fb_ctx_set_msm_split(self._ctx, parts))
 
+    def set_pair_mode(self, mode: int):
+        """commit + open of one row: 0 by size, 1 one batch-of-two MSM, 2 two MSMs on two streams."""
+        self._chk(self._lib.fb_ctx_set_pair_mode(self._ctx, mode))
+
     def join(self):
         """The caller's stream waits (on the device) for every dev_* call in flight on the lanes."""
         self._chk(self._lib.fb_ctx_join(self._ctx))
@@ -268,6 +272,24 @@ class PianoBackend:
                                          C.addressof(ys), C.addressof(pis)))
         return ([ys.raw[k * 32:(k + 1) * 32] for k in range(nrows)],
                 [pis.raw[k * 48:(k + 1) * 48] for k in range(nrows)])
+
+    def commit_open_rows(self, row0: int, nrows: int, coeffs: ScalarVec, alpha) -> Tuple[List[bytes], List[bytes], List[bytes]]:
+        """commit_rows + open_rows in one call (one upload) -> (commitments, evaluations, proofs)."""
+        buf, n = pack_scalars(coeffs)
+        if nrows == 0 or n % nrows:
+            raise FourierError(2, "coefficient count is not a multiple of the row count")
+        a = pack_scalar(alpha)
+        cs = C.create_string_buffer(G1_BYTES * nrows)
+        ys = C.create_string_buffer(FR_BYTES * nrows)
+        pis = C.create_string_buffer(G1_BYTES * nrows)
+        self._chk(self._lib.fb_commit_open_rows(self._ctx, row0, nrows, _lib.addr(buf), n // nrows, _lib.addr(a),
+                                                C.addressof(cs), C.addressof(ys), C.addressof(pis)))
+        return ([cs.raw[k * 48:(k + 1) * 48] for k in range(nrows)], [ys.raw[k * 32:(k + 1) * 32] for k in range(nrows)],
+                [pis.raw[k * 48:(k + 1) * 48] for k in range(nrows)])
+
+    def dev_commit_open_rows(self, row0: int, nrows: int, d_coeffs, length: int, d_alpha, d_out48s, d_out_ys, d_out_proofs):
+        self._chk(self._lib.fb_dev_commit_open_rows(self._ctx, row0, nrows, _lib.addr(d_coeffs), length, _lib.addr(d_alpha),
+                                                    _lib.addr(d_out48s), _lib.addr(d_out_ys), _lib.addr(d_out_proofs)))
 
     # -- column shards (one MSM over several GPUs) ----------------------------------
     def set_col_shard(self, col0: int, ncols: int):

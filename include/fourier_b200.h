@@ -83,6 +83,10 @@ int fb_ctx_set_open_mode(fb_ctx* ctx, int mode);
  * `parts` streams of its lane, so that one sub-MSM's latency-bound phases run under another's multiplier-bound
  * ones; the partial sums are added on the device.  Same bytes as parts = 1 (default). */
 int fb_ctx_set_msm_split(fb_ctx* ctx, int parts);
+/* how the two MSMs of a commit + open of one row run (fb_*_commit_open*): 0 (default) by size - rows of >= 2^18 points as
+ * two MSMs on two streams of the call's lane, smaller ones as one batch-of-two pass; 1 always the batch; 2 always two
+ * streams.  Same bytes. */
+int fb_ctx_set_pair_mode(fb_ctx* ctx, int mode);
 /* uploads from PAGEABLE host memory (a Rust Vec<u8>, Python bytes): 0 (default) copy
  * through the lane's pinned double buffer, 1 hand the pointer to cudaMemcpyAsync.
  * Pinned / registered sources are always copied directly. */
@@ -128,6 +132,11 @@ int fb_commit_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* co
                    uint8_t* out48s);
 int fb_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len,
                  const uint8_t alpha_be[32], uint8_t* out_ys_be, uint8_t* out_proof48s);
+
+/* commit + open of rows [row0, row0+nrows) in one call (extension): the matrix goes up once, the commit MSMs overlap the
+ * field half and the proof MSMs.  Byte-identical to fb_commit_rows + fb_open_rows.  len must be a power of two. */
+int fb_commit_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const uint8_t* coeffs_be, uint64_t len,
+                        const uint8_t alpha_be[32], uint8_t* out_commit48s, uint8_t* out_ys_be, uint8_t* out_proof48s);
 
 /* partial results over the resident column range (uncompressed, 96 bytes); the
  * coefficient vector is always the FULL row */
@@ -270,6 +279,9 @@ int fb_dev_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d_c
  * address up (cudaGetSymbolAddress): make one call before beginning a graph capture. */
 int fb_dev_evaluate_noalloc(int device, const void* d_poly_fr, uint64_t len, const void* d_x_fr, void* d_out_y_fr,
                             void* cuda_stream);
+
+int fb_dev_commit_open_rows(fb_ctx* ctx, uint64_t row0, uint64_t nrows, const void* d_coeffs_fr, uint64_t len,
+                            const void* d_alpha_fr, void* d_out_commit48s, void* d_out_ys_be, void* d_out_proof48s);
 
 /* number of kernel launches issued by this library so far */
 uint64_t fb_launch_count(const fb_ctx* ctx);

@@ -360,6 +360,7 @@ def test_c5_bivariate_rows_full_size(gpu):
     alpha, beta = int.from_bytes(alpha_b, "big"), int.from_bytes(beta_b, "big")
     commits = b.commit_rows(0, M, coeffs)
     ys, pis = b.open_rows(0, M, coeffs, alpha_b)
+    assert b.commit_open_rows(0, M, coeffs, alpha_b) == (commits, ys, pis)
     sample = sorted({0, 1, 2, 3, 17, 255, 256, 511, 512, 513, 700, 767, 1000, 1021, 1022, 1023})
     for i in sample:
         row = synth.fr_ints(51, T, i * T)
@@ -445,6 +446,11 @@ def test_split_msm_same_bytes(gpu, n, m):
     coeffs = synth.fr_bytes(91, M * T)
     alpha_b = synth.fr_bytes(92, 1).tobytes()
     want = (b.commit_rows(0, M, coeffs), b.open_rows(0, M, coeffs, alpha_b))
+    for mode in (0, 1):  # the fused rows call: commit MSMs on a sub-stream / everything on one stream
+        b.set_pair_mode(mode)
+        cs, ys, ps = b.commit_open_rows(0, M, coeffs, alpha_b)
+        assert (cs, (ys, ps)) == want
+    b.set_pair_mode(0)
     want_fused = b.worker_commit_open(M - 1, coeffs[(M - 1) * T:], alpha_b)
     assert want_fused == (want[0][M - 1], want[1][0][M - 1], want[1][1][M - 1])
     for parts in (2, 3, 4):
@@ -453,6 +459,10 @@ def test_split_msm_same_bytes(gpu, n, m):
             assert (b.commit_rows(0, M, coeffs), b.open_rows(0, M, coeffs, alpha_b)) == want
             assert b.worker_commit_open(M - 1, coeffs[(M - 1) * T:], alpha_b) == want_fused
     b.set_msm_split(1)
+    for mode in (1, 2, 0):  # the fused pair as one batch of two, as two MSMs on two streams, by size
+        b.set_pair_mode(mode)
+        for _ in range(2):
+            assert b.worker_commit_open(M - 1, coeffs[(M - 1) * T:], alpha_b) == want_fused
     if m == 0:
         o = known_tau_oracle(n, 0)
         assert want[0][0] == bls.g1_compress(o.worker_commit_known_tau(0, synth.fr_ints(91, T)))
