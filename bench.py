@@ -352,7 +352,7 @@ def own_arm(args):
             "roofline": {"kernel": "whole MSM pipeline (digits, sort, batched-affine rounds, XYZZ accumulate, bucket reduction), "
                                    "both MSMs of the step", "bound": "int",
                          "achieved": ach_mad / 1e12, "peak": int_peak / 1e12, "unit": "T wide-MAD/s", "frac": ach_mad / int_peak,
-                         "frac_real": frac_real, "peak_source": int_src,
+                         "frac_real": frac_real, "frac_real_step": muls_step / (ms_dev * 1e-3) / fp_mul_rate, "peak_source": int_src,
                          "traffic": sum(traffic.values()) * 2 if traffic else None,
                          "work": "%d wide-MAD/point at the fixed accounting window (SURVEY 8d) x %d points" % (mad_pp, pts_step),
                          "real_work": {"fp_muls_per_step": muls_step, "affine_round_slots": slots, "xyzz_survivors": surv,
@@ -361,7 +361,9 @@ def own_arm(args):
                          "dominant_kernel": {"name": PHASE_KERNELS.get(dom, dom), "ms_per_step": dom_ms,
                                              "share_of_step": dom_ms / step_ms_prof if step_ms_prof else None,
                                              "frac_real": dom_real if dom == "msm.round_pass2" else None},
-                         "note": "frac credits 10 Fp multiplies per (point, window) whatever the kernels spend (they spend 6 in the "
+                         "note": "frac_real is measured on the profiled single-stream run (phases_ms_per_step); frac_real_step divides the same "
+                                 "multiply count by the timed step (value), in which the two MSMs overlap.  "
+                                 "frac credits 10 Fp multiplies per (point, window) whatever the kernels spend (they spend 6 in the "
                                  "affine rounds), so it is a work-equivalent rate; frac_real is multiplier utilisation: Fp multiplies "
                                  "issued / time / the fe_mul microbenchmark rate.  traffic = dram bytes of the round kernels of both "
                                  "MSMs from the ncu capture in profiles/ (r1 geometry)"},
