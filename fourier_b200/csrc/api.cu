@@ -304,7 +304,9 @@ void fb_ctx_destroy(fb_ctx* c) {
     if (c->d_g_tau_x) cudaFree(c->d_g_tau_x);
     if (c->d_g_tau_y) cudaFree(c->d_g_tau_y);
     if (c->u_bases.pts && c->u_bases.pts != c->d_u) cudaFree(c->u_bases.pts);
+    if (c->u_bases.xs) cudaFree((void*)c->u_bases.xs);
     if (c->y_bases.pts && c->y_bases.pts != c->d_g_tau_y) cudaFree(c->y_bases.pts);
+    if (c->y_bases.xs) cudaFree((void*)c->y_bases.xs);
     if (c->d_u) cudaFree(c->d_u);
     c->shard_buf.release();
     c->shard_coeffs.release();
@@ -578,6 +580,9 @@ int fb_bases_precompute(fb_ctx* c, fb_bases* b, int window_bits) {
         msm_build_table(b->raw, b->b.n, 1, cc, nwin, tab, L->pt_a, L->stream);
         FB_CUDA(cudaStreamSynchronize(L->stream));
         if (b->b.pts != b->raw) cudaFree(b->b.pts);
+        if (b->b.xs) cudaFree((void*)b->b.xs);
+        b->b.xs = msm_alloc_xtable(tab, (size_t)nwin * b->b.n, L->stream);
+        FB_CUDA(cudaStreamSynchronize(L->stream));
         b->b.pts = tab;
         b->b.c = cc;
         b->b.nwin = nwin;
@@ -596,6 +601,7 @@ void fb_bases_free(fb_ctx* c, fb_bases* b) {
     if (!b) return;
     if (c) cudaSetDevice(c->device);
     if (b->b.pts && b->b.pts != b->raw) cudaFree(b->b.pts);
+    if (b->b.xs) cudaFree((void*)b->b.xs);
     if (b->raw) cudaFree(b->raw);
     delete b;
 }

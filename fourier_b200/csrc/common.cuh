@@ -146,6 +146,7 @@ struct MsmBases {
     size_t n = 0;             // row length
     int c = 0;                // window bits of the table (0: no table)
     int nwin = 0;
+    const char* xs = nullptr;  // optional: the x coordinates alone, one 64-byte slot per table entry (same indexing)
     uint32_t stride() const { return c > 0 ? kTableStride : (uint32_t)sizeof(G1Affine); }
 };
 
@@ -182,6 +183,8 @@ void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_
 // table construction: out[row][w][k] = 2^(c*w) * in[row][k], w < nwin, kTableStride bytes per entry
 void msm_build_table(const G1Affine* d_in, size_t n, size_t rows, int c, int nwin, void* d_out, DevBuf& scratch,
                      cudaStream_t st);
+// a copy of the table's x coordinates in 64-byte slots for MsmBases::xs (cudaMalloc'ed; nullptr if disabled or out of memory)
+const char* msm_alloc_xtable(const void* d_table, size_t entries, cudaStream_t st);
 int msm_pick_window(size_t n, bool tabulated);
 int msm_num_windows(int c);  // ceil(255 / c)
 

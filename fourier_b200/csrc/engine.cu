@@ -1,6 +1,7 @@
 // engine.cu - the PianoBackend calls of the C ABI: SRS residency and the
 // worker / master commit + open paths (reference src/engine/piano.rs:143-298,
 // 587-846, 883-1037).
+#include <stdlib.h>
 #include <string.h>
 
 #include <fstream>
@@ -22,7 +23,9 @@ namespace {
 
 void srs_free(fb_ctx* c) {
     if (c->u_bases.pts && c->u_bases.pts != c->d_u) cudaFree(c->u_bases.pts);
+    if (c->u_bases.xs) cudaFree((void*)c->u_bases.xs);
     if (c->y_bases.pts && c->y_bases.pts != c->d_g_tau_y) cudaFree(c->y_bases.pts);
+    if (c->y_bases.xs) cudaFree((void*)c->y_bases.xs);
     if (c->d_u) cudaFree(c->d_u);
     if (c->d_g_tau_x) cudaFree(c->d_g_tau_x);
     if (c->d_g_tau_y) cudaFree(c->d_g_tau_y);
@@ -51,6 +54,7 @@ void srs_build_tables(fb_ctx* c, fb_lane* L) {
         c->u_bases.pts = tab;
         c->u_bases.c = cc;
         c->u_bases.nwin = nwin;
+        c->u_bases.xs = msm_alloc_xtable(tab, (size_t)nwin * c->ncols * c->nrows, L->stream);
     }
     if (c->M >= 16) {
         int cc = msm_pick_window(c->M, true);
@@ -61,6 +65,7 @@ void srs_build_tables(fb_ctx* c, fb_lane* L) {
         c->y_bases.pts = tab;
         c->y_bases.c = cc;
         c->y_bases.nwin = nwin;
+        c->y_bases.xs = msm_alloc_xtable(tab, (size_t)nwin * c->M, L->stream);
     }
     FB_CUDA(cudaStreamSynchronize(L->stream));
 }
@@ -80,6 +85,7 @@ MsmBases row_bases(fb_ctx* c, uint64_t i) {
     MsmBases b = c->u_bases;
     size_t per_row = (size_t)(b.c > 0 ? b.nwin : 1) * c->ncols;
     b.pts = (char*)c->u_bases.pts + (i - c->row0) * per_row * b.stride();
+    if (b.xs) b.xs += (i - c->row0) * per_row * 64;
     return b;
 }
 

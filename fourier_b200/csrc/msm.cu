@@ -204,6 +204,7 @@ __device__ __forceinline__ G1Affine load_point(const char* pts, uint32_t stride,
 //   pass 2  walks the slots backwards, peels off each pair's inverse and writes the sum.
 // After a few rounds the survivors (a few per bucket) go through the XYZZ kernel below.
 struct RoundArgs {
+    const char* xs;           // GATHER, optional: x coordinates at 64-byte stride (pass 1 reads these instead of the lines)
     const char* pts;          // GATHER: the resident table; else the previous round's output (bucket order)
     uint32_t stride;          // bytes per input point (128 in a table, 96 otherwise)
     const uint32_t* off_out;  // [nbuckets + 1] bucket offsets of the output, off_out[b+1]-off_out[b] = ceil(count_in/2)
@@ -341,9 +342,14 @@ struct SlotX {
     uint2 d;
     Fp x1, x2;
 };
-__device__ __forceinline__ void slot_x_load(const char* pts, uint32_t stride, uint2 d, SlotX& s) {
+__device__ __forceinline__ void slot_x_load(const char* pts, uint32_t stride, uint2 d, SlotX& s, const char* xs = nullptr) {
     s.d = d;
     if (d.y == kNone) return;
+    if (xs) {
+        s.x1 = ldg_fp(reinterpret_cast<const Fp*>(xs + (size_t)(d.x & 0x7fffffffu) * 64));
+        s.x2 = ldg_fp(reinterpret_cast<const Fp*>(xs + (size_t)(d.y & 0x7fffffffu) * 64));
+        return;
+    }
     s.x1 = ldg_fp(&point_at(pts, stride, d.x)->x);
     s.x2 = ldg_fp(&point_at(pts, stride, d.y)->x);
 }
@@ -389,10 +395,11 @@ __device__ __forceinline__ void round_pass1_body(const RoundArgs& a) {
         }
     } else {
         SlotX nxt;
-        if (ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + lane), nxt);
+        const char* xs = MODE == 2 ? a.xs : nullptr;
+        if (ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + lane), nxt, xs);
         for (uint32_t j = 0; j < ws.cnt; j++) {
             const SlotX cur = nxt;
-            if (j + 1 < ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + 32u * (j + 1) + lane), nxt);
+            if (j + 1 < ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + 32u * (j + 1) + lane), nxt, xs);
             run = fe_mul<F>(run, slot_x_den(a.pts, a.stride, cur));
             a.pref[(size_t)j * nt + t] = run;
         }
@@ -767,6 +774,35 @@ __global__ void __launch_bounds__(32) k_sum_parts(const G1Xyzz* __restrict__ par
 
 }  // namespace
 
+__global__ void __launch_bounds__(256) k_build_xtable(const char* __restrict__ table, size_t entries, uint4* __restrict__ xs) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // one 16-byte chunk per thread, 4 per entry
+    if (i >= entries * 4) return;
+    const size_t e = i >> 2, c = i & 3;
+    xs[i] = c < 3 ? reinterpret_cast<const uint4*>(table + e * kTableStride)[c] : make_uint4(0, 0, 0, 0);
+}
+// The x coordinates of a window table once more, alone, in 64-byte slots.  The first round's pass 1 needs x only; out of the
+// 128-byte table lines the whole line travels (2.07 GB per 2^20-point MSM), out of this copy one 64-byte DRAM atom does:
+// pass 1 2.71 -> 2.46 ms per step, step 10.89 -> 10.68 ms (profiles/r2_v6_ab_xtable.txt), for +50 % table memory.
+// Tables above 4 GiB (the 2^24-point MSM: 25.8 GB; the 2^10 rows: 11.8 GB) measured no gain (pass 1 16.1 ms / 11.2 ms either
+// way), so the copy is built for tables of <= 2^25 entries only.  FB_MSM_XTAB=0 turns it off, =2 forces it; nullptr when off
+// or when the memory is not there (the MSM then reads the lines).
+const char* msm_alloc_xtable(const void* d_table, size_t entries, cudaStream_t st) {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("FB_MSM_XTAB");
+        on = e ? atoi(e) : 1;
+    }
+    if (!on || !entries || (on == 1 && entries > ((size_t)1 << 25))) return nullptr;
+    void* xs = nullptr;
+    if (cudaMalloc(&xs, entries * 64) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    (++fb::g_launches, k_build_xtable<<<(unsigned)((entries * 4 + 255) / 256), 256, 0, st>>>((const char*)d_table, entries, (uint4*)xs));
+    FB_CUDA(cudaGetLastError());
+    return (const char*)xs;
+}
+
 int msm_num_windows(int c) { return (255 + c - 1) / c; }  // scalars are recoded below 2^254 (k_digits)
 
 // Window width by a cost model in Fp multiplications: n*W mixed additions (10 each) plus
@@ -949,6 +985,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         const uint32_t rnt = blocks * rthreads;
         RoundArgs ra;
         ra.pts = pts_cur;
+        ra.xs = (r == 0 && tab) ? bases.xs : nullptr;
         ra.stride = stride_cur;
         ra.off_out = off_out;
         ra.nbuckets = nbuckets;
@@ -1129,12 +1166,14 @@ void msm_run_split(const MsmBases& bases, const Fr* d_scalars, size_t len, size_
             const size_t r0 = batch * k / S, r1 = batch * (k + 1) / S;
             MsmBases b = bases;
             b.pts = (char*)bases.pts + r0 * per_row * bases.stride();
+            if (bases.xs) b.xs = bases.xs + r0 * per_row * 64;
             msm_run(b, d_scalars + r0 * len, len, r1 - r0, scalars_mont, d_out + r0, *ex.scratch[k], st);
         } else {
             const int v = k / col_parts, q = k % col_parts;
             const size_t c0 = len * q / col_parts, c1 = len * (q + 1) / col_parts;
             MsmBases b = bases;
             b.pts = (char*)bases.pts + c0 * bases.stride();  // index = w * bases.n + column: shifting the base shifts the column
+            if (bases.xs) b.xs = bases.xs + c0 * 64;
             msm_run(b, (v ? d_scalars2 : d_scalars) + c0, c1 - c0, 1, scalars_mont, parts + k, *ex.scratch[k], st);
         }
         if (k) {

@@ -46,7 +46,7 @@ def test_reference_kat_on_gpu(gpu):
 
 
 @pytest.mark.parametrize("log_n", [14, 20, 22])
-def test_ntt_and_open_scalars_vs_c_oracle(gpu, log_n):
+def test_ntt_vs_c_oracle(gpu, log_n):
     from fourier_b200 import PianoBackend, synth
     from oracle import cref
     n = 1 << log_n
