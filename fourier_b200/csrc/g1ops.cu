@@ -120,20 +120,17 @@ __global__ void __launch_bounds__(128) k_sum_xyzz(const G1Xyzz* __restrict__ in,
     out[t] = acc;
 }
 
-// parts: nparts x (96 | 32 | 96) bytes; thread 0 adds the commitments' partials, thread 1 the proofs'; y is every
-// part's (they agree) and is copied from part 0.  out: 48 | 32 | 48.
+// parts: nparts x (96 | 32 | 96) bytes; y is every part's (they agree) and is copied from part 0.  out: 48 | 32 | 48.
+// One warp: lane t takes kind t & 1 (0 the commitments' partials, 1 the proofs') of parts t >> 1, t >> 1 + 16, ...;
+// the lanes of one kind then add up in a shared-memory tree - log2(nparts) dependent additions instead of nparts.
 __global__ void __launch_bounds__(32) k_combine_parts(const uint8_t* __restrict__ parts, size_t nparts, uint8_t* __restrict__ out,
                                                       int* err) {
-    const int t = threadIdx.x;
-    if (t >= 2) {
-        if (t == 2)
-            for (int k = 0; k < 32; k++) out[48 + k] = parts[96 + k];
-        return;
-    }
+    __shared__ G1Xyzz sm[32];
+    const int t = threadIdx.x, kind = t & 1;
     G1Xyzz acc = G1Xyzz::inf();
-    for (size_t p = 0; p < nparts; p++) {
+    for (size_t p = t >> 1; p < nparts; p += 16) {
         uint8_t buf[96];
-        const uint8_t* src = parts + p * 224 + (t ? 128 : 0);
+        const uint8_t* src = parts + p * 224 + (kind ? 128 : 0);
         for (int k = 0; k < 96; k++) buf[k] = src[k];
         G1Affine q;
         int rc = g1_deserialize(buf, &q);
@@ -143,6 +140,20 @@ __global__ void __launch_bounds__(32) k_combine_parts(const uint8_t* __restrict_
         }
         g1_add_mixed(acc, q);
     }
+    sm[t] = acc;
+    for (int s = 16; s >= 2; s >>= 1) {
+        __syncwarp();
+        if (t < s) {
+            G1Xyzz x = sm[t];
+            g1_add(x, sm[t + s]);  // t and t + s are of one kind: s is even
+            sm[t] = x;
+        }
+    }
+    __syncwarp();
+    if (t == 2)
+        for (int k = 0; k < 32; k++) out[48 + k] = parts[96 + k];
+    if (t >= 2) return;
+    acc = sm[t];
     G1Affine r = acc.is_inf() ? G1Affine::inf() : g1_to_affine_with_inv(acc, fe_inv_gcd<FpParams>(acc.zzz));
     uint8_t o[48];
     g1_compress(r, o);
