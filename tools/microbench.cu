@@ -230,6 +230,18 @@ int main() {
         MULB("fr_mul", FrParams, 0, 1, 128)
         MULB("fr_mul", FrParams, 0, 2, 128)
         MULB("fr_mul", FrParams, 1, 1, 128)
+        // rate of dependent fe_mul<Fp> chains against warps per SM sub-partition (one CTA per SM of 4*k warps): where the
+        // multiplier saturates, and whether two independent chains per thread (ilp 2) reach it with fewer warps
+#define OCC(ilp, k)                                                                                                 \
+    {                                                                                                              \
+        float ms = time_ms([&] { k_mul_loop<FpParams, 0, ilp><<<sms, 128 * k>>>((Fp*)da, iters); });               \
+        double muls = (double)sms * 128 * k * iters * ilp;                                                         \
+        printf("{\"bench\": \"fp_mul_occupancy\", \"warps_per_smsp\": %d, \"ilp\": %d, \"ms\": %.3f, \"gmul_per_s\": %.2f}\n", k, ilp, \
+               ms, muls / ms / 1e6);                                                                               \
+    }
+        OCC(1, 1) OCC(1, 2) OCC(1, 3) OCC(1, 4) OCC(1, 6) OCC(1, 8)
+        OCC(2, 1) OCC(2, 2) OCC(2, 3) OCC(2, 4)
+        OCC(4, 1) OCC(4, 2)
         // inversion latency: 148 x 5 CTAs x 4 warps, one lane each
         {
             const int nw = sms * 20;
