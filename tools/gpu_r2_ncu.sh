@@ -23,6 +23,7 @@ python tools/ncu_summary.py launches gpurun_out/launches.csv > gpurun_out/${NCU_
 for f in gpurun_out/*.ncu-rep; do
   [ -f "$f" ] || continue
   python tools/ncu_summary.py full $f > ${f%.ncu-rep}.txt 2>/dev/null
+  python tools/ncu_summary.py source $f > ${f%.ncu-rep}_source.txt 2>/dev/null
   sz=$(stat -c %s $f); if [ $sz -gt 25000000 ]; then rm -f $f; echo "dropped $f ($sz bytes; summary kept)"; fi
 done
 ls -la gpurun_out/

@@ -3,6 +3,8 @@
 
   python tools/ncu_summary.py launches gpurun_out/launches.csv          > profiles/<name>.txt
   python tools/ncu_summary.py full gpurun_out/prof.ncu-rep [metric ...] > profiles/<name>.txt
+  python tools/ncu_summary.py source gpurun_out/prof.ncu-rep [regex]     > profiles/<name>.txt
+      (warp-state samples of each captured kernel by source line and by SASS opcode; needs -lineinfo and --import-source on)
 """
 import collections
 import csv
@@ -64,6 +66,90 @@ def launches(path):
         print("%-44s %6d %12.3f %8.2f %12.1f" % (k[:44], a[0], a[1] / 1e6, 100 * a[1] / tot, a[1] / a[0] / 1e3))
 
 
+def source(path, pattern):
+    """Per kernel in the report: where the sampled warps were (source line, stall reason, SASS opcode)."""
+    out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True,
+                         text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    kernels = []  # (name, header, body rows)
+    i = 0
+    cur_file = None
+    while i < len(rows):
+        r = rows[i]
+        if len(r) == 2 and r[0] == "File Path":
+            cur_file = r[1]
+        elif len(r) == 2 and r[0] == "Function Name":
+            kernels.append([r[1], cur_file, None, []])
+        elif r and r[0] == "Line No" and kernels:
+            kernels[-1][2] = r
+        elif kernels and kernels[-1][2] is not None and len(r) == len(kernels[-1][2]):
+            kernels[-1][3].append(r)
+        i += 1
+    # the page has one section per (kernel instance, source file): merge the sections of one instance
+    merged = []
+    for name, fpath, hdr, body in kernels:
+        if merged and merged[-1][0] == name and fpath not in merged[-1][1]:
+            merged[-1][1].append(fpath)
+            merged[-1][2].append((fpath, hdr, body))
+        else:
+            merged.append([name, [fpath], [(fpath, hdr, body)]])
+    for name, files, sections in merged:
+        if pattern and not re.search(pattern, name):
+            continue
+        by_line = collections.Counter()
+        by_line_stall = collections.defaultdict(collections.Counter)
+        by_op = collections.Counter()
+        by_op_stall = collections.defaultdict(collections.Counter)
+        by_stall = collections.Counter()
+        by_file = collections.Counter()
+        line_src = {}
+        total = 0
+        for fpath, hdr, body in sections:
+            short = fpath.rsplit("/", 1)[-1]
+            col = {h: k for k, h in enumerate(hdr)}
+            ci_samp = col.get("# Samples")
+            stall_cols = [(h, k) for k, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
+            cur_line = None
+            for r in body:
+                if r[0] != "":  # a source line; the SASS rows that follow carry its samples (counted once, from SASS)
+                    cur_line = "%s:%s" % (short, r[0])
+                    line_src[cur_line] = r[1].strip()[:80]
+                    continue
+                try:
+                    n = int(r[ci_samp])
+                except (ValueError, TypeError):
+                    continue
+                if not n:
+                    continue
+                total += n
+                op = r[3].strip().split()
+                op = (op[1] if op and op[0].startswith("@") and len(op) > 1 else (op[0] if op else "?"))
+                by_line[cur_line] += n
+                by_op[op] += n
+                by_file[short] += n
+                for h, k in stall_cols:
+                    try:
+                        v = int(r[k])
+                    except ValueError:
+                        v = 0
+                    if v:
+                        by_stall[h] += v
+                        by_line_stall[cur_line][h] += v
+                        by_op_stall[op][h] += v
+        pct = lambda v: 100.0 * v / max(total, 1)
+        print("--- %s" % name[:120])
+        print("  warp-state samples %d;  by file: %s" % (total, ", ".join("%s %.1f%%" % (f, pct(v)) for f, v in by_file.most_common(6))))
+        print("  by stall reason: " + ", ".join("%s %.1f%%" % (h[6:], pct(v)) for h, v in by_stall.most_common(10)))
+        print("  by SASS opcode (top 16):")
+        for op, n in by_op.most_common(16):
+            top = ", ".join("%s %.1f" % (h[6:], pct(v)) for h, v in by_op_stall[op].most_common(4))
+            print("    %-22s %5.1f%%   %s" % (op, pct(n), top))
+        print("  by source line (top 24):")
+        for ln, n in by_line.most_common(24):
+            top = ", ".join("%s %.1f" % (h[6:], pct(v)) for h, v in by_line_stall[ln].most_common(3))
+            print("    %-20s %5.1f%%   %-80s %s" % (ln, pct(n), line_src.get(ln, ""), top))
+
+
 def full(path, extra):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -77,7 +163,9 @@ def full(path, extra):
 
 
 if __name__ == "__main__":
-    if sys.argv[1] == "launches":
+    if sys.argv[1] == "source":
+        source(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
+    elif sys.argv[1] == "launches":
         launches(sys.argv[2])
     else:
         full(sys.argv[2], sys.argv[3:])
