@@ -366,7 +366,7 @@ def own_arm(args):
                                  "frac credits 10 Fp multiplies per (point, window) whatever the kernels spend (they spend 6 in the "
                                  "affine rounds), so it is a work-equivalent rate; frac_real is multiplier utilisation: Fp multiplies "
                                  "issued / time / the fe_mul microbenchmark rate.  traffic = dram bytes of the round kernels of both "
-                                 "MSMs from the ncu capture in profiles/ (r1 geometry)"},
+                                 "MSMs from the ncu capture in profiles/ (traffic.json: r2_v7_ncu_round_kernels.txt)"},
             "roofline_hbm": {"kernel": PHASE_KERNELS.get(dom, dom), "bound": "hbm", "achieved": ach_gbs, "peak": peaks["hbm_gbs"],
                              "unit": "GB/s", "frac": ach_gbs / peaks["hbm_gbs"], "traffic": traffic.get(dom),
                              "peak_source": peaks["source"],
