@@ -1079,6 +1079,10 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         G1Xyzz* col_buf[2] = {arena + nbuckets, arena + nbuckets + nbuckets / 2};
         const G1Xyzz* rin = buckets;
         const G1Xyzz* cin = buckets;
+        static const uint64_t fold_wide = [] {  // FB_MSM_FOLD_WIDE: outputs of a pass from which it folds four inputs per thread
+            const char* e = getenv("FB_MSM_FOLD_WIDE");
+            return e ? (uint64_t)atoll(e) : (uint64_t)kNumSMs * 4 * 32 * 2;  // two warps per scheduler
+        }();
         uint32_t rl = 1u << l;  // remaining row length (row sums shrink it to 1)
         uint32_t ch = 1u << h;  // remaining column height
         int pp = 0;
@@ -1087,8 +1091,11 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
             fa.d[0] = FoldDir{rin, row_buf[pp], 0, 1, 1};
             fa.d[1] = FoldDir{cin, col_buf[pp], 0, 1, 1};
             uint32_t mx = 0;
+            // four inputs per output (three dependent additions per thread) while the pass has enough warps to keep the
+            // multipliers busy; two per output (one addition, twice the threads, one more pass) once it does not - a
+            // thread's additions are sequential, so the narrow passes are shorter as a tree
             if (rl > 1) {
-                uint32_t G = rl >= 4 ? 4 : 2;
+                uint32_t G = (rl >= 4 && (uint64_t)nsets * (1u << h) * (rl / 4) >= fold_wide) ? 4 : 2;
                 rl /= G;
                 fa.d[0].G = G;
                 fa.d[0].L = 1;
@@ -1097,7 +1104,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
                 mx = fa.d[0].n_out;
             }
             if (ch > 1) {
-                uint32_t G = ch >= 4 ? 4 : 2;
+                uint32_t G = (ch >= 4 && (uint64_t)nsets * (ch / 4) * (1u << l) >= fold_wide) ? 4 : 2;
                 ch /= G;
                 fa.d[1].G = G;
                 fa.d[1].L = 1u << l;
