@@ -891,11 +891,12 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     // round is bound by the gather); small inputs do not amortise the per-round inversion.
     // Jobs of >= 64 M entries (the 2^24-point MSM, the 2^10 batched rows) amortise two more rounds when the buckets
     // are deep enough: 2^24 points 217.5 -> 222.1 Mpts/s, bivariate rows 69.1 -> 67.8 ms; at 2^20 points (16 M
-    // entries) a fourth round costs 0.1 ms (profiles/r1_v7_sweeps.txt).
+    // entries) a fourth round costs 0.1 ms (profiles/r1_v7_sweeps.txt).  Round 2 (profiles/r2_v7_rounds_sweep.txt): at 2^24 points
+    // (96 entries per bucket) 5 / 6 / 7 / 8 rounds give 232.1 / 231.3 / 235.8 / 233.8 Mpts/s, three runs each.
     int rounds = 0;
     if (entries >= (4u << 20) && entries / nbuckets >= 8) {
         rounds = 3;
-        if (entries >= (64u << 20) && entries / nbuckets >= 64) rounds = 5;
+        if (entries >= (64u << 20) && entries / nbuckets >= 64) rounds = 7;  // one survivor per bucket: the XYZZ pass and its combine all but vanish
         else if (entries >= (64u << 20) && entries / nbuckets >= 32) rounds = 4;
     }
     if (rounds_env >= 0) rounds = rounds_env;
