@@ -364,8 +364,8 @@ FB_HD Fe<P> fe_inv(const Fe<P>& a) {  // a^(m-2); inv(0) = 0
     return fe_pow<P, P::N>(a, e);
 }
 
-// Low-latency inversion for ONE element on ONE thread (the XYZZ -> affine step of a
-// single MSM result): Kaliski's almost-Montgomery inverse, a binary extended GCD of
+// Low-latency inversion for ONE element on ONE thread (the per-CTA inversion of the affine rounds and of the opening's
+// denominators): Kaliski's almost-Montgomery inverse, a binary extended GCD of
 // <= 2*bits shift/subtract rounds on the limbs, instead of the ~1.5*bits dependent
 // Montgomery multiplies of Fermat's a^(m-2).  Input and output in Montgomery form;
 // inv(0) = 0.  Data-dependent branches: use fe_inv (branch-free) in warp-wide code.
@@ -454,6 +454,154 @@ FB_HD Fe<P> fe_inv_gcd(const Fe<P>& a) {
     x = fe_mul<P>(x, b);
     for (int i = 0; i < rem; i++) x = fe_dbl<P>(x);
     return x;
+}
+
+// Inversion by the Bernstein-Yang division steps ("safegcd", ia.cr/2019/266), in the batched form libsecp256k1's
+// modinv32 popularised: 30 division steps at a time on the low words of f and g build a 2x2 transition matrix, which is then
+// applied once to the full-width f, g (exact division by 2^30) and to d, e (division by 2^30 modulo m).  Signed 30-bit
+// limbs; the outer loop runs until g == 0 (data-dependent; the inputs here are not secret).  Input and output in
+// Montgomery form; inv(0) = 0.
+// Measured against fe_inv_gcd (profiles/r2_v7_ab_inversion.txt): about the same instruction count, but on the wide-MAD pipe
+// instead of the ALU.  Alone on the GPU it is 1.4x faster (XYZZ -> affine of a result: 71 -> 27 us); under a concurrent
+// multiplier-bound kernel it is slower, which is where the per-CTA inversions of the affine rounds run.  So: this one for
+// the end-of-call steps (k_to_affine, k_combine_parts), fe_inv_gcd inside the rounds and the opening.
+template <class P>
+FB_HD Fe<P> fe_inv_safegcd(const Fe<P>& a) {
+    constexpr int N = P::N;
+    constexpr int L = (32 * N + 29) / 30 + (((32 * N) % 30 == 0) ? 1 : 0);  // limbs of 30 bits incl. room for the sign: 13 (Fp), 9 (Fr)
+    constexpr int32_t M30 = (int32_t)(0xffffffffu >> 2);
+    if (a.is_zero()) return a;
+    auto to30 = [](const uint32_t* x, int32_t* out) {
+#pragma unroll
+        for (int j = 0; j < L; j++) {
+            const int bit = 30 * j, w = bit >> 5, off = bit & 31;
+            uint32_t lo = w < N ? x[w] : 0u;
+            uint32_t hi = (w + 1 < N) ? x[w + 1] : 0u;
+            uint32_t v = off ? ((lo >> off) | (hi << (32 - off))) : lo;
+            out[j] = (int32_t)(v & (uint32_t)M30);
+        }
+    };
+    int32_t m[L], f[L], g[L], d[L], e[L];
+    {
+        uint32_t mw[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) mw[i] = P::mod(i);
+        to30(mw, m);
+        to30(a.v, g);
+    }
+#pragma unroll
+    for (int i = 0; i < L; i++) {
+        f[i] = m[i];
+        d[i] = 0;
+        e[i] = 0;
+    }
+    e[0] = 1;
+    const uint32_t minv30 = (0u - P::INV) & (uint32_t)M30;  // m^-1 mod 2^30
+    int32_t zeta = -1;  // -(delta + 1/2), delta = 1/2
+    for (int iter = 0; iter < 64; iter++) {  // <= 30 batches for 384-bit inputs; the bound is a backstop
+        // 30 division steps on the low words; [[u, v], [q, r]] / 2^30 maps (f, g) to the new (f, g)
+        uint32_t u = 1, v = 0, q = 0, r = 1;
+        {
+            uint32_t fl = (uint32_t)f[0] | ((uint32_t)f[1] << 30), gl = (uint32_t)g[0] | ((uint32_t)g[1] << 30);
+#pragma unroll 6
+            for (int i = 0; i < 30; i++) {
+                const uint32_t c1 = (uint32_t)(zeta >> 31);
+                const uint32_t c2 = 0u - (gl & 1u);
+                const uint32_t x = (fl ^ c1) - c1, y = (u ^ c1) - c1, z = (v ^ c1) - c1;
+                gl += x & c2;
+                q += y & c2;
+                r += z & c2;
+                const uint32_t c3 = c1 & c2;
+                zeta = (int32_t)((uint32_t)zeta ^ c3) - 1;
+                fl += gl & c3;
+                u += q & c3;
+                v += r & c3;
+                gl >>= 1;
+                u <<= 1;
+                v <<= 1;
+            }
+        }
+        const int32_t su = (int32_t)u, sv = (int32_t)v, sq = (int32_t)q, sr = (int32_t)r;
+        // (d, e) <- [[u, v], [q, r]] (d, e) / 2^30 mod m, kept in (-2m, m)
+        {
+            const int32_t sd = d[L - 1] >> 31, se = e[L - 1] >> 31;
+            int32_t md = (su & sd) + (sv & se);
+            int32_t me = (sq & sd) + (sr & se);
+            long long cd = (long long)su * d[0] + (long long)sv * e[0];
+            long long ce = (long long)sq * d[0] + (long long)sr * e[0];
+            md -= (int32_t)((minv30 * (uint32_t)cd + (uint32_t)md) & (uint32_t)M30);
+            me -= (int32_t)((minv30 * (uint32_t)ce + (uint32_t)me) & (uint32_t)M30);
+            cd += (long long)m[0] * md;
+            ce += (long long)m[0] * me;
+            cd >>= 30;
+            ce >>= 30;
+#pragma unroll
+            for (int i = 1; i < L; i++) {
+                cd += (long long)su * d[i] + (long long)sv * e[i] + (long long)m[i] * md;
+                ce += (long long)sq * d[i] + (long long)sr * e[i] + (long long)m[i] * me;
+                d[i - 1] = (int32_t)cd & M30;
+                e[i - 1] = (int32_t)ce & M30;
+                cd >>= 30;
+                ce >>= 30;
+            }
+            d[L - 1] = (int32_t)cd;
+            e[L - 1] = (int32_t)ce;
+        }
+        // (f, g) <- [[u, v], [q, r]] (f, g) / 2^30, exactly
+        {
+            long long cf = (long long)su * f[0] + (long long)sv * g[0];
+            long long cg = (long long)sq * f[0] + (long long)sr * g[0];
+            cf >>= 30;
+            cg >>= 30;
+#pragma unroll
+            for (int i = 1; i < L; i++) {
+                cf += (long long)su * f[i] + (long long)sv * g[i];
+                cg += (long long)sq * f[i] + (long long)sr * g[i];
+                f[i - 1] = (int32_t)cf & M30;
+                g[i - 1] = (int32_t)cg & M30;
+                cf >>= 30;
+                cg >>= 30;
+            }
+            f[L - 1] = (int32_t)cf;
+            g[L - 1] = (int32_t)cg;
+        }
+        int32_t gz = 0;
+#pragma unroll
+        for (int i = 0; i < L; i++) gz |= g[i];
+        if (gz == 0) break;
+    }
+    // f = +-1 and d = +- 1/a: negate by the sign of f and bring d from (-2m, m) to [0, m)
+    {
+        const int32_t neg = f[L - 1] >> 31;
+        int32_t add = d[L - 1] >> 31;
+#pragma unroll
+        for (int i = 0; i < L; i++) d[i] = ((d[i] + (m[i] & add)) ^ neg) - neg;
+#pragma unroll
+        for (int i = 0; i < L - 1; i++) {
+            d[i + 1] += d[i] >> 30;
+            d[i] &= M30;
+        }
+        add = d[L - 1] >> 31;
+#pragma unroll
+        for (int i = 0; i < L; i++) d[i] += m[i] & add;
+#pragma unroll
+        for (int i = 0; i < L - 1; i++) {
+            d[i + 1] += d[i] >> 30;
+            d[i] &= M30;
+        }
+    }
+    Fe<P> x;
+#pragma unroll
+    for (int i = 0; i < N; i++) {  // word i = bits [32 i, 32 i + 32) of sum d[j] 2^(30 j)
+        const int bit = 32 * i, j = bit / 30, off = bit % 30;
+        uint32_t w = (uint32_t)d[j] >> off;
+        if (j + 1 < L) w |= (uint32_t)d[j + 1] << (30 - off);
+        if (off > 28 && j + 2 < L) w |= (uint32_t)d[j + 2] << (60 - off);
+        x.v[i] = w;
+    }
+    // the input was A = a R (as an integer), x = 1 / A = R^-1 / a; the Montgomery form of 1 / a is x R^2: two products with R^2
+    x = fe_mul<P>(x, Fe<P>::rsquared());
+    return fe_mul<P>(x, Fe<P>::rsquared());
 }
 
 using Fr = Fe<FrParams>;

@@ -66,13 +66,13 @@ __global__ void __launch_bounds__(128) k_to_affine(const G1Xyzz* __restrict__ in
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     // few results, one inversion each: the latency of the dependent chain is what
-    // counts here, so the binary-GCD inversion (fe_inv_gcd) replaces Fermat's ladder
+    // counts here, so the division-step inversion (fe_inv_safegcd) replaces Fermat's ladder
     const G1Xyzz p = in[i];
     if (p.is_inf()) {
         out[i] = G1Affine::inf();
         return;
     }
-    out[i] = g1_to_affine_with_inv(p, fe_inv_gcd<FpParams>(p.zzz));
+    out[i] = g1_to_affine_with_inv(p, fe_inv_safegcd<FpParams>(p.zzz));
 }
 
 // generator comb: tab[w*255 + d-1] = d * 2^(8w) * G  (w < 32, 1 <= d <= 255)
@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(32) k_combine_parts(const uint8_t* __restrict_
         for (int k = 0; k < 32; k++) out[48 + k] = parts[96 + k];
     if (t >= 2) return;
     acc = sm[t];
-    G1Affine r = acc.is_inf() ? G1Affine::inf() : g1_to_affine_with_inv(acc, fe_inv_gcd<FpParams>(acc.zzz));
+    G1Affine r = acc.is_inf() ? G1Affine::inf() : g1_to_affine_with_inv(acc, fe_inv_safegcd<FpParams>(acc.zzz));
     uint8_t o[48];
     g1_compress(r, o);
     uint8_t* dst = out + (t ? 80 : 0);

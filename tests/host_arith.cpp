@@ -64,6 +64,7 @@ void h_fr_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
         case 3: z = fe_inv<FrParams>(x); break;
         case 4: z = fe_to_mont<FrParams>(x); break;
         case 6: z = fe_inv_gcd<FrParams>(x); break;
+        case 7: z = fe_inv_safegcd<FrParams>(x); break;
         default: z = fe_from_mont<FrParams>(x); break;
     }
     memcpy(r, z.v, 32);
@@ -79,6 +80,7 @@ void h_fp_op(int op, const uint32_t* a, const uint32_t* b, uint32_t* r) {
         case 3: z = fe_inv<FpParams>(x); break;
         case 4: z = fe_to_mont<FpParams>(x); break;
         case 6: z = fe_inv_gcd<FpParams>(x); break;
+        case 7: z = fe_inv_safegcd<FpParams>(x); break;
         default: z = fe_from_mont<FpParams>(x); break;
     }
     memcpy(r, z.v, 48);

@@ -77,10 +77,17 @@ def test_field_ops(L, name, m, n):
         assert val(r) == a * RR % m
         op(5, arr(a, n), arr(b, n), r)
         assert val(r) == a * Ri % m
-    # binary-GCD inversion (the single-result XYZZ -> affine path) == Fermat == big-int
-    for a, b in cases[:600] + [(k, 0) for k in (2, 3, m - 2, (m - 1) // 2, (m + 1) // 2)]:
+    # single-thread inversions (shift-and-subtract, op 6; division-step batches, op 7) == Fermat == big-int
+    edge = [2, 3, m - 2, (m - 1) // 2, (m + 1) // 2, 1 << 30, (1 << 30) - 1, 1 << 60, (1 << (32 * n - 3)) % m,
+            RR % m, Ri, (m - RR) % m, pow(2, 32 * n - 1, m)]
+    edge += [(1 << k) % m for k in range(1, 32 * n, 29)] + [(m - (1 << k)) % m for k in range(0, 32 * n - 4, 31)]
+    inv_cases = cases[:2500] + [(k, 0) for k in edge]
+    for a, b in inv_cases[:600] + inv_cases[-60:]:
         op(6, arr(a, n), arr(b, n), r)
-        assert val(r) == (pow(a * Ri % m, -1, m) * RR % m if a else 0)
+        assert val(r) == (pow(a * Ri % m, -1, m) * RR % m if a else 0), hex(a)
+    for a, b in inv_cases:
+        op(7, arr(a, n), arr(b, n), r)
+        assert val(r) == (pow(a * Ri % m, -1, m) * RR % m if a else 0), hex(a)
 
 
 def cb(b):

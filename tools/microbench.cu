@@ -99,10 +99,10 @@ __global__ void k_madd_loop(G1Affine* pts, G1Xyzz* out, int iters, int npts) {
 
 // latency of ONE binary-GCD inversion on ONE lane per warp (how the batched-affine rounds and the
 // evaluation-form opening use it): every warp inverts its own element, 20 warps per SM
-template <class P>
+template <class P, int ALG = 0>  // ALG 0: fe_inv_gcd (shift-and-subtract, ALU pipe), 1: fe_inv_safegcd (division-step batches, wide MADs)
 __global__ void k_inv_lane0(Fe<P>* data) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if ((threadIdx.x & 31) == 0) data[warp] = fe_inv_gcd<P>(data[warp]);
+    if ((threadIdx.x & 31) == 0) data[warp] = ALG ? fe_inv_safegcd<P>(data[warp]) : fe_inv_gcd<P>(data[warp]);
 }
 
 template <class P>
@@ -252,6 +252,19 @@ int main() {
             printf("{\"bench\": \"fe_inv_gcd<Fp> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
             ms = time_ms([&] { k_inv_lane0<FrParams><<<sms * 5, 128>>>((Fr*)dinv); });
             printf("{\"bench\": \"fe_inv_gcd<Fr> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FpParams, 1><<<sms * 5, 128>>>(dinv); });
+            printf("{\"bench\": \"fe_inv_safegcd<Fp> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FrParams, 1><<<sms * 5, 128>>>((Fr*)dinv); });
+            printf("{\"bench\": \"fe_inv_safegcd<Fr> one lane per warp, 20 warps/SM\", \"ms\": %.4f}\n", ms);
+            // one warp per SM: the latency of a lone inversion (how the end-of-call steps see it)
+            ms = time_ms([&] { k_inv_lane0<FpParams, 0><<<sms, 32>>>(dinv); });
+            printf("{\"bench\": \"fe_inv_gcd<Fp> one lane, one warp per SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FpParams, 1><<<sms, 32>>>(dinv); });
+            printf("{\"bench\": \"fe_inv_safegcd<Fp> one lane, one warp per SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FrParams, 0><<<sms, 32>>>((Fr*)dinv); });
+            printf("{\"bench\": \"fe_inv_gcd<Fr> one lane, one warp per SM\", \"ms\": %.4f}\n", ms);
+            ms = time_ms([&] { k_inv_lane0<FrParams, 1><<<sms, 32>>>((Fr*)dinv); });
+            printf("{\"bench\": \"fe_inv_safegcd<Fr> one lane, one warp per SM\", \"ms\": %.4f}\n", ms);
             cudaFree(dinv);
         }
         // mixed additions
