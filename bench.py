@@ -290,7 +290,11 @@ def own_arm(args):
     # ---- per-kernel timing (CUDA events inside the library, on the launching stream) + work counters
     be.profile(True)
     prof_steps = max(1, min(args.steps, 5))
-    prof_fn, prof_sep = (step_sharded, False) if best == "sharded" else (step_fused, False) if fused_best else (step_separate, True)
+    # Which step to profile.  Under profiling every call runs on ONE stream, so the fused call of a row of >= 2^18 points
+    # (timed as two MSMs on two streams) would be profiled as one batch-of-two pass, a pipeline that is not the timed one:
+    # profile the two plain calls instead; smaller rows run the batch-of-two pass when timed, too.
+    fused_prof = fused_best and ncols < (1 << 18)
+    prof_fn, prof_sep = (step_sharded, False) if best == "sharded" else (step_fused, False) if fused_prof else (step_separate, True)
     # one untimed step first: under profiling a call runs on ONE stream (no two-stream pair, no split), whose scratch may
     # have to grow for that shape - allocations in the middle of a step would be charged to whatever phase they interrupt
     prof_fn()
