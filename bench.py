@@ -12,8 +12,9 @@ A "step" = the commitment AND the opening (y, proof) of that polynomial.
                three ways and the best is the headline (config.step says which):
                  separate  fb_dev_worker_commit then fb_dev_worker_open, one stream
                  overlap   the same two calls on two lanes (fb_ctx_set_lanes(2) + join)
-                 fused     fb_dev_worker_commit_open: both MSMs as one batch of two
-                           scalar vectors over the same resident row
+                 fused     fb_dev_worker_commit_open: one call; rows of >= 2^18 points run the two MSMs
+                           on two streams of the lane, smaller rows as one batch of two scalar
+                           vectors over the same resident row
                all three give identical bytes (checked) - extra.step_variants_ms
   e2e          the same through the public host API on HOST buffers (H2D + D2H inside
                the timed region): pinned and pageable sources, separate and fused calls
@@ -338,7 +339,8 @@ def own_arm(args):
             "config": {"workload": WORKLOAD,
                        "step": {"separate": "fb_dev_worker_commit + fb_dev_worker_open, one stream",
                                 "overlap": "fb_dev_worker_commit + fb_dev_worker_open on two lanes (fb_ctx_set_lanes(2)), joined",
-                                "fused": "fb_dev_worker_commit_open (both MSMs as one batch over the same resident row)",
+                                "fused": "fb_dev_worker_commit_open (one call: the two MSMs on two streams of the lane for rows of >= 2^18 points, "
+                                         "one batch of two scalar vectors over the resident row below that)",
                                 "sharded": "fb_dev_commit_open_shard_begin + all-gather of 128-byte states + _finish (field half and "
                                            "MSMs over this rank's slice only)"}[best]
                                + ("" if world == 1 else "; then all-gather of 224-byte partials + fb_dev_combine_commit_open on every rank"),

@@ -341,6 +341,17 @@ int fb_ctx_sync(fb_ctx* c) {
             ctx_join_locked(c);
         }
         ctx_sync_all(c);
+        // The device-resident decoders (fb_dev_fr_from_be, fb_dev_combine_commit_open, ...) are asynchronous: a malformed
+        // scalar or point sets a sticky flag of the caller-stream lane, reported - and cleared - here.
+        fb_lane* U = c->ulane;
+        int flags[2] = {0, 0};
+        FB_CUDA(cudaMemcpy(flags, U->d_err, sizeof(flags), cudaMemcpyDeviceToHost));
+        if (flags[0] || flags[1]) {
+            FB_CUDA(cudaMemset(U->d_err, 0, sizeof(flags)));
+            if (flags[0]) return ctx_fail(c, FB_ERR_SCALAR, "Invalid scalar (in an earlier device-resident call)");
+            return ctx_fail(c, FB_ERR_POINT,
+                            "Failed to uncompress G1 point (code " + std::to_string(flags[1]) + ", in an earlier device-resident call)");
+        }
     } catch (const CudaError& e) {
         cudaGetLastError();
         return ctx_fail(c, FB_ERR_CUDA, e.msg);

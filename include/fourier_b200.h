@@ -59,7 +59,9 @@ const char* fb_version(void);
  * are ordered against S: they see everything enqueued on S before the call, and
  * with the default fb_ctx_set_lanes(1) they simply run on S. */
 int fb_ctx_set_stream(fb_ctx* ctx, void* cuda_stream);
-/* block the host until every lane and S are idle */
+/* block the host until every lane and S are idle.  The device-resident decoders (fb_dev_fr_from_be,
+ * fb_dev_combine_commit_open, the fb_dev_g1_* codecs) cannot fail synchronously: a scalar >= r or a malformed point sets
+ * a sticky flag, and this call returns FB_ERR_SCALAR / FB_ERR_POINT for it (once; the flag is cleared). */
 int fb_ctx_sync(fb_ctx* ctx);
 /* lanes >= 2: the heavy device-resident calls (fb_dev_worker_commit / _open /
  * _commit_open, fb_dev_commit_rows / _open_rows, fb_dev_msm*, and the _partial

@@ -72,6 +72,54 @@ def test_column_shards_sum_to_the_unsharded_result(gpu, n, shards):
     full.close()
 
 
+@pytest.mark.parametrize("nparts", [1, 2, 5, 16, 17, 40])
+def test_device_combine_of_many_parts(gpu, nparts):
+    """fb_dev_combine_commit_open on arbitrary 224-byte records (96-byte point | y | 96-byte point): the kernel deserialises
+    the parts in parallel (16 per kind at a time) and adds them as a tree.  Parts include the identity, a repeated point
+    (P + P inside the tree) and a point with its negative; more parts than one sweep of the warp (17, 40)."""
+    import torch
+    from fourier_b200 import PianoBackend
+    rng = random.Random(900 + nparts)
+    be = PianoBackend(4, 0)
+    ss = [rng.randrange(1, R) for _ in range(nparts)]
+    ts = [rng.randrange(1, R) for _ in range(nparts)]
+    if nparts >= 5:
+        ss[1] = ss[0]              # P + P
+        ss[2] = 0                  # identity
+        ts[3] = (R - ts[4]) % R    # Q and -Q
+    if nparts >= 17:
+        ss[16] = ss[0]             # meets part 0 again, in the second sweep of the same lane
+    y = rng.randrange(R).to_bytes(32, "big")
+    rec = b"".join(bls.g1_serialize(bls.g1_mul(bls.G1_GEN, s)) + y + bls.g1_serialize(bls.g1_mul(bls.G1_GEN, t))
+                   for s, t in zip(ss, ts))
+    dev = torch.device("cuda", 0)
+    d_parts = torch.frombuffer(bytearray(rec), dtype=torch.uint8).to(dev)
+    d_out = torch.zeros(128, dtype=torch.uint8, device=dev)
+    be.dev_combine_commit_open(d_parts, nparts, d_out)
+    be.sync()
+    want = (bls.g1_compress(bls.g1_mul(bls.G1_GEN, sum(ss) % R)) + y + bls.g1_compress(bls.g1_mul(bls.G1_GEN, sum(ts) % R)))
+    assert bytes(d_out.cpu().numpy()) == want
+    # a part that is not on the curve is rejected
+    bad = bytearray(rec)
+    bad[95] ^= 1
+    d_bad = torch.frombuffer(bad, dtype=torch.uint8).to(dev)
+    from fourier_b200 import FourierError
+    be.dev_combine_commit_open(d_bad, nparts, d_out)  # asynchronous: the call itself cannot know
+    with pytest.raises(FourierError) as ei:
+        be.sync()                                     # ... fb_ctx_sync reports the sticky flag, once
+    assert "G1 point" in str(ei.value)
+    be.sync()
+    if nparts == 1:  # the same for a scalar >= r through the device-resident decoder
+        d_in = torch.frombuffer(bytearray(R.to_bytes(32, "big") + (5).to_bytes(32, "big")), dtype=torch.uint8).to(dev)
+        d_fr = torch.zeros(64, dtype=torch.uint8, device=dev)
+        be.dev_fr_from_be(d_in, d_fr, 2)
+        with pytest.raises(FourierError) as ei:
+            be.sync()
+        assert "Invalid scalar" in str(ei.value)
+        be.sync()
+    be.close()
+
+
 @pytest.mark.parametrize("n,length,shards", [(12, 1 << 12, 2), (12, 1 << 12, 3), (14, 1 << 14, 4), (12, 1 << 10, 4), (12, 2, 4), (18, 1 << 18, 8)])
 def test_sharded_field_half_matches_the_unsharded_calls(gpu, n, length, shards):
     """fb_worker_commit_open_shard_begin / _finish: every shard uploads and works on its slice only; the 128-byte states are
