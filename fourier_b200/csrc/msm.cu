@@ -216,6 +216,8 @@ struct RoundArgs {
     uint32_t p_max;           // steps per thread the scratch was sized for
     G1Affine* stage;          // GATHER: [step][thread][2] the two points of each slot, parked by pass 1
     Fp* inv;                  // [thread] inverse of the thread's running product (pass 1 -> pass 2)
+    uint32_t waves;           // pass 2 runs `waves` times the threads of pass 1, each with 1/waves of the steps: a thread of
+                              // pass 1 covers the slots of `waves` consecutive pass-2 warps as that many separate chains
 };
 
 constexpr uint32_t kMinSlots = 16;
@@ -311,9 +313,12 @@ __device__ __forceinline__ int pair_kind(const G1Affine& p1, const G1Affine& p2,
 struct WarpSlots {
     uint32_t base, cnt;  // first slot of the warp; steps of this lane
 };
+__device__ __forceinline__ bool warp_slots_of(const RoundArgs& a, uint32_t O, uint32_t nt, uint32_t t, WarpSlots& ws);
 __device__ __forceinline__ bool warp_slots(const RoundArgs& a, uint32_t O, WarpSlots& ws) {
-    const uint32_t nt = gridDim.x * blockDim.x;
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    return warp_slots_of(a, O, gridDim.x * blockDim.x, blockIdx.x * blockDim.x + threadIdx.x, ws);
+}
+// the slots of thread t of nt (the grid of pass 2)
+__device__ __forceinline__ bool warp_slots_of(const RoundArgs& a, uint32_t O, uint32_t nt, uint32_t t, WarpSlots& ws) {
     const uint32_t lane = threadIdx.x & 31;
     uint32_t P = (O + nt - 1) / nt;
     if (P < kMinSlots) P = kMinSlots;
@@ -376,11 +381,12 @@ __device__ __forceinline__ void round_pass1_body(const RoundArgs& a) {
     const uint32_t nt = gridDim.x * blockDim.x;
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
-    WarpSlots ws;
-    const bool active = warp_slots(a, a.off_out[a.nbuckets], ws);
-    if (!active) ws.base = ws.cnt = 0;  // an idle warp still meets the CTA's barriers below
-    Fp run = Fp::one();
-    if (MODE == 1) {
+    const uint32_t O = a.off_out[a.nbuckets];
+    if (MODE == 1) {  // (waves == 1 on this path)
+        WarpSlots ws;
+        const bool active = warp_slots(a, O, ws);
+        if (!active) ws.base = ws.cnt = 0;  // an idle warp still meets the CTA's barriers below
+        Fp run = Fp::one();
         for (uint32_t j = 0; j < ws.cnt; j++) {
             const uint2 d = slot_desc<true>(a, ws.base + 32u * j + lane);
             Fp den;
@@ -393,20 +399,55 @@ __device__ __forceinline__ void round_pass1_body(const RoundArgs& a) {
             run = fe_mul<F>(run, den);
             a.pref[(size_t)j * nt + t] = run;
         }
-    } else {
+        const Fp r = block_batch_inverse<F, NW>(run);
+        if (active) a.inv[t] = r;
+        return;
+    }
+    // The thread covers the slots of `waves` consecutive warps of pass 2's grid (ntv threads), as that many chains: chain k
+    // restarts its running product (pass 2 peels every chain on its own), leaves its total T_k in inv[tv] and the product
+    // G_k of the totals before it in the spare row of pref; after the CTA's one inversion of G = T_0 ... T_(w-1), a walk
+    // back turns them into 1 / T_k (Montgomery's trick once more, two multiplications per chain).
+    const uint32_t w = a.waves, ntv = nt * w;
+    const uint32_t tv0 = ((t >> 5) * w) * 32u + lane;
+    Fp* gpre = a.pref + (size_t)a.p_max * ntv;
+    const char* xs = MODE == 2 ? a.xs : nullptr;
+    Fp grand = Fp::one();
+    uint32_t live = 0;  // bit k: chain k has steps
+    for (uint32_t k = 0; k < w; k++) {
+        const uint32_t tv = tv0 + 32u * k;
+        WarpSlots ws;
+        if (!warp_slots_of(a, O, ntv, tv, ws) || ws.cnt == 0) continue;
+        live |= 1u << k;
+        Fp run = Fp::one();
         SlotX nxt;
-        const char* xs = MODE == 2 ? a.xs : nullptr;
-        if (ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + lane), nxt, xs);
+        slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + lane), nxt, xs);
         for (uint32_t j = 0; j < ws.cnt; j++) {
             const SlotX cur = nxt;
             if (j + 1 < ws.cnt) slot_x_load(a.pts, a.stride, slot_desc<MODE != 0>(a, ws.base + 32u * (j + 1) + lane), nxt, xs);
             run = fe_mul<F>(run, slot_x_den(a.pts, a.stride, cur));
-            a.pref[(size_t)j * nt + t] = run;
+            a.pref[(size_t)j * ntv + tv] = run;
+        }
+        if (w > 1) {
+            gpre[tv] = grand;
+            a.inv[tv] = run;
+            grand = fe_mul<F>(grand, run);
+        } else {
+            grand = run;
         }
     }
     // one inversion per CTA (4 warps): 176 -> ~80 us per launch against one per warp (batchinv.cuh)
-    const Fp r = block_batch_inverse<F, NW>(run);
-    if (active) a.inv[t] = r;
+    Fp r = block_batch_inverse<F, NW>(grand);
+    if (w == 1) {
+        if (live) a.inv[tv0] = r;
+        return;
+    }
+    for (uint32_t k = w; k-- > 0;) {
+        if (!(live >> k & 1u)) continue;
+        const uint32_t tv = tv0 + 32u * k;
+        const Fp tk = a.inv[tv];
+        a.inv[tv] = fe_mul<F>(r, gpre[tv]);
+        r = fe_mul<F>(r, tk);
+    }
 }
 
 // MODE 0: streamed input; 1: the points parked by pass 1; 2: gather through the slot map
@@ -978,12 +1019,39 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
             (++fb::g_launches, k_halve_counts<<<(nbuckets + 256) / 256, 256, 0, st>>>(off_cur, nbuckets, cnt_tmp));
             exclusive_scan(cnt_tmp, off_out, nbuckets + 1, s.block_sums, st);
         }
+        // Pass 1 runs one wave of CTAs (each pays one inversion on one lane while its other warps wait); pass 2 runs `waves`
+        // times as many CTAs with 1 / waves of the steps each: one wave gives every warp the same number of steps, but the
+        // warps of a scheduler do not advance evenly and the last ones run alone (ncu: 12.8 of 16 warps resident on
+        // average); with several waves a finished CTA is replaced.  Every chain costs pass 1 three more multiplications
+        // and a restart of its load pipeline, so chains keep >= 24 steps: up to 6 waves (profiles/r2_v8_ab_waves.txt: 2^24-point
+        // MSM 235.9 -> 243.9 Mpts/s at 6, the 2^10 x 2^12 rows 58.4 -> 57.7 ms, the headline step 12.46 -> 12.34 ms on one
+        // stream and unchanged when its two MSMs overlap).  FB_MSM_WAVES=k fixes the number (1: the single-wave form).
+        static const uint32_t waves_env = [] {
+            const char* e = getenv("FB_MSM_WAVES");
+            int v = e ? atoi(e) : 0;
+            return (uint32_t)(v < 0 ? 0 : (v > 16 ? 16 : v));
+        }();
+        static const int regather = [] {
+            // First round: pass 1 reads the x coordinates only (two sectors per point) and pass 2, which is
+            // multiplier-bound, hides a second gather of the full points; FB_MSM_REGATHER=0 parks the
+            // points in pass 1 instead (measured 4% slower at 2^20; L2 prefetches made both slower).
+            const char* e = getenv("FB_MSM_REGATHER");
+            return e ? atoi(e) : 1;
+        }();
         uint32_t blocks = (uint32_t)(kNumSMs * round_blocks_per_sm);
+        uint32_t waves = waves_env;
         {
-            uint64_t need = (ub_out / kMinSlots + rthreads - 1) / rthreads + 1;
+            uint64_t need = (ub_out / kMinSlots + rthreads - 1) / rthreads + 1;  // CTAs of pass 2 with >= kMinSlots steps per thread
             if (need < blocks) blocks = (uint32_t)need;
+            if (!waves) {  // by size: chains of >= 24 steps
+                const uint64_t steps = ub_out / ((uint64_t)blocks * rthreads);
+                waves = (uint32_t)(steps / 24 < 1 ? 1 : (steps / 24 > 6 ? 6 : steps / 24));
+            }
+            if (r == 0 && !regather) waves = 1;
+            while (waves > 1 && (uint64_t)blocks * waves > need) waves--;
         }
-        const uint32_t rnt = blocks * rthreads;
+        const uint32_t blocks2 = blocks * waves;
+        const uint32_t rnt = blocks2 * rthreads;  // threads of pass 2
         RoundArgs ra;
         ra.pts = pts_cur;
         ra.xs = (r == 0 && tab) ? bases.xs : nullptr;
@@ -994,7 +1062,8 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         uint64_t p_max = (ub_out + rnt - 1) / rnt;
         if (p_max < kMinSlots) p_max = kMinSlots;
         ra.p_max = (uint32_t)p_max;
-        ra.pref = s.pref.as<Fp>(p_max * rnt);
+        ra.pref = s.pref.as<Fp>((p_max + 1) * rnt);  // + one row: the products of the chain totals (pass 1)
+        ra.waves = waves;
         uint32_t* wbuf = s.where.as<uint32_t>(2 * ub_out);
         ra.where = wbuf;
         ra.where2 = reinterpret_cast<const uint2*>(wbuf);
@@ -1003,25 +1072,17 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         ra.inv = s.inv.as<Fp>(rnt);
         ra.stage = nullptr;
         if (r == 0) {
-            // Default: pass 1 reads the x coordinates only (two sectors per point) and pass 2, which is
-            // multiplier-bound, hides a second gather of the full points; FB_MSM_REGATHER=0 parks the
-            // points in pass 1 instead (measured 4% slower at 2^20; L2 prefetches made both slower).
-            static int regather = -1;
-            if (regather < 0) {
-                const char* e = getenv("FB_MSM_REGATHER");
-                regather = e ? atoi(e) : 1;
-            }
             if (!direct) (++fb::g_launches, k_slot_map<true><<<(unsigned)mb, 256, 0, st>>>(off_cur, off_out, nbuckets, sorted, wbuf, reinterpret_cast<uint2*>(wbuf)));
             prof_mark("msm.round_pass1", st);
             if (regather) {
                 (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<2><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<2><<<blocks, 128, 0, st>>>(ra)));
                 prof_mark("msm.round_pass2", st);
-                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<2><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<2><<<blocks, 128, 0, st>>>(ra)));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<2><<<blocks2, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<2><<<blocks2, 128, 0, st>>>(ra)));
             } else {
                 ra.stage = s.stage.as<G1Affine>(2 * p_max * rnt);
                 (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<1><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<1><<<blocks, 128, 0, st>>>(ra)));
                 prof_mark("msm.round_pass2", st);
-                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<1><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<1><<<blocks, 128, 0, st>>>(ra)));
+                (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<1><<<blocks2, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<1><<<blocks2, 128, 0, st>>>(ra)));
             }
         } else {
             {
@@ -1032,7 +1093,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
             prof_mark("msm.round_pass1", st);
             (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass1_w6<0><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass1<0><<<blocks, 128, 0, st>>>(ra)));
             prof_mark("msm.round_pass2", st);
-            (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<0><<<blocks, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<0><<<blocks, 128, 0, st>>>(ra)));
+            (round_warps == 6 ? (void)(++fb::g_launches, k_round_pass2_w6<0><<<blocks2, 192, 0, st>>>(ra)) : (void)(++fb::g_launches, k_round_pass2<0><<<blocks2, 128, 0, st>>>(ra)));
         }
         if (stats_on) k_stat_add<<<1, 1, 0, st>>>(stats, 2, off_out + nbuckets, 0);
         pts_cur = reinterpret_cast<const char*>(ra.out);
