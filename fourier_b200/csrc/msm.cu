@@ -1023,7 +1023,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         // times as many CTAs with 1 / waves of the steps each: one wave gives every warp the same number of steps, but the
         // warps of a scheduler do not advance evenly and the last ones run alone (ncu: 12.8 of 16 warps resident on
         // average); with several waves a finished CTA is replaced.  Every chain costs pass 1 three more multiplications
-        // and a restart of its load pipeline, so chains keep >= 24 steps: up to 6 waves (profiles/r2_v8_ab_waves.txt: 2^24-point
+        // and a restart of its load pipeline, so chains keep a minimum length: up to 6 waves (profiles/r2_v8_ab_waves.txt: 2^24-point
         // MSM 235.9 -> 243.9 Mpts/s at 6, the 2^10 x 2^12 rows 58.4 -> 57.7 ms, the headline step 12.46 -> 12.34 ms on one
         // stream and unchanged when its two MSMs overlap).  FB_MSM_WAVES=k fixes the number (1: the single-wave form).
         static const uint32_t waves_env = [] {
@@ -1043,9 +1043,11 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
         {
             uint64_t need = (ub_out / kMinSlots + rthreads - 1) / rthreads + 1;  // CTAs of pass 2 with >= kMinSlots steps per thread
             if (need < blocks) blocks = (uint32_t)need;
-            if (!waves) {  // by size: chains of >= 24 steps
-                const uint64_t steps = ub_out / ((uint64_t)blocks * rthreads);
-                waves = (uint32_t)(steps / 24 < 1 ? 1 : (steps / 24 > 6 ? 6 : steps / 24));
+            if (!waves) {  // by size: chains of >= 24 steps in the first round, whose pass 1 waits for its gather anyway, of >= 64
+                           // in the streamed rounds, where the chains' extra multiplications show (ncu, profiles/r2_v9_*: two
+                           // chains of 24 cost the second round's pass 1 more than its pass 2 gained)
+                const uint64_t steps = ub_out / ((uint64_t)blocks * rthreads), per = r == 0 ? 24 : 64;
+                waves = (uint32_t)(steps / per < 1 ? 1 : (steps / per > 6 ? 6 : steps / per));
             }
             if (r == 0 && !regather) waves = 1;
             while (waves > 1 && (uint64_t)blocks * waves > need) waves--;
