@@ -15,7 +15,27 @@ def expect(ss, ks):
     return bls.g1_compress(bls.g1_mul(bls.G1_GEN, sum(s * k for s, k in zip(ss, ks)) % R))
 
 
+def large():
+    """A 2^20-point MSM with a table against its known discrete log: the size at which a forced FB_MSM_WAVES takes effect
+    (smaller jobs fall back to one chain per thread)."""
+    from fourier_b200 import synth
+    be = PianoBackend(4, 0)
+    n = 1 << 20
+    bases = be.bases_from_scalars(synth.fr_bytes(41, n))
+    bases.precompute()
+    got = be.msm(bases, synth.fr_bytes(42, n))
+    assert got == expect(synth.fr_ints(41, n), synth.fr_ints(42, n))
+    # skewed scalars: a few very deep buckets, many single-entry ones
+    ks = [(k * k) % 1000 for k in range(n)]
+    assert be.msm(bases, ks) == expect(synth.fr_ints(41, n), ks)
+    bases.free()
+    be.close()
+    print("ok 2")
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "large":
+        return large()
     rng = random.Random(2024)
     be = PianoBackend(4, 0)
     n = 512

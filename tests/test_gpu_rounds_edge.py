@@ -31,3 +31,16 @@ def test_round_kernels_on_special_slots(gpu, env):
                        timeout=600, cwd=os.path.dirname(HERE))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert r.stdout.strip().splitlines()[-1].startswith("ok ")
+
+
+@pytest.mark.parametrize("waves", [1, 2, 3, 5, 6])
+def test_round_kernels_chains_per_thread(gpu, waves):
+    """Pass 2 of the rounds on `waves` times the grid of pass 1 (FB_MSM_WAVES forced): pass 1 walks each thread's slots as
+    that many chains and derives every chain's inverse from the CTA's one inversion.  2^20 points (smaller jobs clamp to one
+    chain), random and skewed scalars, known discrete logs."""
+    e = dict(os.environ)
+    e["FB_MSM_WAVES"] = str(waves)
+    r = subprocess.run([sys.executable, os.path.join(HERE, "rounds_edge_check.py"), "large"], env=e, capture_output=True,
+                       text=True, timeout=900, cwd=os.path.dirname(HERE))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.strip().splitlines()[-1].startswith("ok ")
