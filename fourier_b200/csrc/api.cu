@@ -170,6 +170,7 @@ void lane_msm(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_scalars,
               const Fr* d_scalars2) {
     const int S = (g_prof && g_prof->on) ? 1 : c->msm_split;  // per-phase timing needs one stream
     if (S <= 1) {
+        L->msm.overlapped = !(g_prof && g_prof->on) && c->async_lanes > 1 && L != c->ulane;  // heavy calls rotate over lanes
         msm_run(bases, d_scalars, len, batch, true, d_out, L->msm, L->stream, d_scalars2);
         return;
     }
@@ -194,6 +195,7 @@ bool lane_pair_fork(fb_ctx* c, fb_lane* L, const MsmBases& bases, const Fr* d_a,
     if (!two) return false;
     FB_CUDA(cudaEventRecord(L->sub_fork, L->stream));
     FB_CUDA(cudaStreamWaitEvent(L->sub_stream[0], L->sub_fork, 0));
+    L->msm_sub[0].overlapped = true;
     msm_run(bases, d_a, cnt, 1, true, d_r, L->msm_sub[0], L->sub_stream[0]);
     FB_CUDA(cudaEventRecord(L->sub_join[0], L->sub_stream[0]));
     return true;
@@ -204,7 +206,9 @@ void lane_pair_join(fb_ctx* c, fb_lane* L, bool forked, const MsmBases& bases, c
         lane_msm(c, L, bases, d_a, cnt, 2, d_r, d_b);
         return;
     }
+    L->msm.overlapped = true;
     msm_run(bases, d_b, cnt, 1, true, d_r + 1, L->msm, L->stream);
+    L->msm.overlapped = false;
     FB_CUDA(cudaStreamWaitEvent(L->stream, L->sub_join[0], 0));
 }
 

@@ -156,6 +156,10 @@ struct MsmScratch {
     // through the XYZZ accumulation, [4] buckets  (u64 each; fb_msm_stats)
     DevBuf stats;
     bool stats_zeroed = false;
+    // set by the caller when another MSM runs next to this one (the two streams of a commit + open pair, calls rotating over
+    // several lanes): one more affine round then pays - the rounds fill the multiplier better than the XYZZ pass they shorten,
+    // which only shows when something else can use the gaps (profiles/r2_v7_rounds_sweep.txt, r2_v9_ab_rounds_overlap.txt)
+    bool overlapped = false;
 };
 
 // d_out[b] (device XYZZ) = sum_k scalars[b*len + k] * bases_b[k] for b < batch, where

@@ -936,7 +936,7 @@ void msm_run(const MsmBases& bases, const Fr* d_scalars, size_t len, size_t batc
     // (96 entries per bucket) 5 / 6 / 7 / 8 rounds give 232.1 / 231.3 / 235.8 / 233.8 Mpts/s, three runs each.
     int rounds = 0;
     if (entries >= (4u << 20) && entries / nbuckets >= 8) {
-        rounds = 3;
+        rounds = (s.overlapped && entries >= (8u << 20)) ? 4 : 3;
         if (entries >= (64u << 20) && entries / nbuckets >= 64) rounds = 7;  // one survivor per bucket: the XYZZ pass and its combine all but vanish
         else if (entries >= (64u << 20) && entries / nbuckets >= 32) rounds = 4;
     }
